@@ -1,0 +1,133 @@
+// common.cuh -- shared host-side state of libpcd_b200 (context, cloud, scratch, error plumbing).
+// Product code: never includes or links anything under oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include <mutex>
+#include "../../include/pcd_b200.h"
+
+namespace pcd {
+
+void set_global_error(const std::string& s);
+
+// Grow-only device buffer.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) { cudaFree(p); p = nullptr; cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+    cudaError_t e = cudaMallocHost(&p, bytes);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Uniform-grid NN index view passed by value to kernels.
+struct GridView {
+  const float4* pts;            // cell-sorted: x, y, z, __int_as_float(original index)
+  const uint32_t* cell_start;   // n_cells + 1 offsets into pts
+  float ox, oy, oz;             // origin = bbox min
+  float c, inv_c;               // cell edge (power of two) and its reciprocal
+  int dx, dy, dz;               // grid dimensions (x fastest)
+  float margin_cells;           // conservative slack (in cells) for float cell assignment
+  uint32_t n;
+};
+
+// 1 m sub-map of PcdProj::BuildSubMap, cell-sorted.
+struct SubmapView {
+  const int32_t* keys;          // 3 per cell, lexicographic order
+  const uint32_t* start;        // n_cells + 1
+  const float4* pts;            // x, y, z, original index; insertion order inside a cell
+  int64_t n_cells;
+  float len, height, width;
+};
+
+}  // namespace pcd
+
+struct pcd_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;       // used by the host-pointer entry points
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  cudaEvent_t ev[8] = {};
+  std::string err;
+  int64_t launches = 0;
+  int64_t counters[4] = {0, 0, 0, 0};
+  int sm_count = 148;
+  // scratch for the batched search (one batch in flight per context)
+  pcd::DevBuf keys, keys_alt, vals, vals_alt, cub_tmp, misc, partial;
+  pcd::DevBuf stage_in[2], stage_out[2], stage_aux[2];
+  pcd::PinBuf pin_in[2], pin_out[2];
+  pcd::DevBuf img_buf, feat_buf, zbuf, sel_buf;
+};
+
+struct pcd_cloud {
+  pcd_ctx* ctx = nullptr;
+  int64_t n = 0;
+  float* aos = nullptr;                // AoS8, post-swap, index space
+  // NN grid
+  bool has_index = false;
+  float4* grid_pts = nullptr;
+  uint32_t* cell_start = nullptr;
+  pcd::GridView grid = {};
+  int64_t n_cells = 0;
+  float bb_lo[3] = {0, 0, 0}, bb_hi[3] = {0, 0, 0};
+  // sub-map
+  bool has_submap = false;
+  pcd_proj_options opt = {};
+  int32_t* sub_keys = nullptr;
+  uint32_t* sub_start = nullptr;
+  float4* sub_pts = nullptr;
+  int64_t sub_cells = 0;
+};
+
+#define PCD_FAIL(ctx_, code_, ...)                                   \
+  do {                                                               \
+    char _b[512];                                                    \
+    snprintf(_b, sizeof _b, __VA_ARGS__);                            \
+    if (ctx_) (ctx_)->err = _b;                                      \
+    pcd::set_global_error(_b);                                       \
+    return (code_);                                                  \
+  } while (0)
+
+#define PCD_CUDA(ctx_, expr_)                                                            \
+  do {                                                                                   \
+    cudaError_t _e = (expr_);                                                            \
+    if (_e != cudaSuccess)                                                               \
+      PCD_FAIL(ctx_, PCD_E_CUDA, "CUDA error %s at %s:%d (%s)", cudaGetErrorString(_e),  \
+               __FILE__, __LINE__, #expr_);                                              \
+  } while (0)
+
+#define PCD_LAUNCH_CHECK(ctx_)                                                           \
+  do {                                                                                   \
+    (ctx_)->launches++;                                                                  \
+    PCD_CUDA(ctx_, cudaGetLastError());                                                  \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+static inline int pcd_blocks(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }

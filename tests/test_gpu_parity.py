@@ -1,0 +1,355 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.  All tests need a B200."""
+import os
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5   # north_star: residuals / Jacobians / fp64 record fields within 1e-5 relative
+
+
+def _close(a, b, tol=REL_TOL):
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    both_nan = np.isnan(a) & np.isnan(b)
+    ok = both_nan | (np.abs(a - b) <= tol * np.maximum(np.abs(a), np.abs(b)) + 1e-300)
+    return bool(ok.all())
+
+
+@pytest.fixture(scope="module")
+def scene(orc, synth, pcd, ctx):
+    raw, info = synth.make_cloud(300_000, seed=synth.SEED0)
+    world = orc.direction_trans(raw)
+    cloud = pcd.Cloud(ctx, raw, direction_trans=True)
+    cloud.build_index()
+    q, opt_num = synth.make_queries(world, 40_000)
+    tree = orc.KdTree(world)
+    yield dict(raw=raw, world=world, cloud=cloud, q=q, opt_num=opt_num, tree=tree, info=info)
+    cloud.close()
+
+
+# ---------------------------------------------------------------- loader (a1, a2) ----------
+def test_direction_trans_and_nan_drop(scene):
+    got = scene["cloud"].download()
+    assert got.shape == scene["world"].shape
+    assert np.array_equal(got.view(np.uint32), scene["world"].view(np.uint32))   # bit-exact incl. -0.0
+
+
+def test_ply_roundtrip_and_load(tmp_path, scene, pcd, ctx, orc):
+    raw = scene["raw"][:5000]
+    for binary in (True, False):
+        path = str(tmp_path / f"c{int(binary)}.ply")
+        pcd.ply_write(path, raw, binary=binary)
+        back = pcd.ply_read(path)
+        assert np.array_equal(np.isnan(back), np.isnan(raw))
+        assert np.array_equal(np.nan_to_num(back), np.nan_to_num(raw))
+        cl = pcd.Cloud.load_ply(ctx, path, pcd.ProjOptions.default())
+        assert np.array_equal(np.nan_to_num(cl.download()), np.nan_to_num(orc.direction_trans(raw)))
+        cl.close()
+    with pytest.raises(pcd.PcdError):
+        pcd.Cloud.load_ply(ctx, str(tmp_path / "missing.ply"))
+
+
+# ---------------------------------------------------------------- NN (a3-a5) ---------------
+def test_nn_unbounded_bit_exact(scene, orc):
+    idx, d2 = scene["cloud"].nn(scene["q"])
+    oi, od = scene["tree"].nn(scene["q"])
+    assert np.array_equal(idx, oi)
+    assert np.array_equal(d2.view(np.uint32), od.view(np.uint32))
+    # the kd-tree oracle itself against exhaustive search on a slice
+    bi, bd = orc.nn_brute(scene["world"], scene["q"][:1500])
+    assert np.array_equal(bi, oi[:1500]) and np.array_equal(bd, od[:1500])
+
+
+def test_nn_radius_semantics(scene, orc):
+    rng = orc.search_range(scene["opt_num"])          # 14 distinct radii 1.5 .. 0.2
+    assert len(np.unique(rng)) == 14
+    idx, d2 = scene["cloud"].nn(scene["q"], rng)
+    oi, _ = scene["tree"].nn(scene["q"])
+    l = scene["world"][oi, 0:3].astype(np.float64) - scene["q"]
+    dist = np.sqrt(l[:, 0] ** 2 + (l[:, 1] ** 2 + l[:, 2] ** 2))
+    want = np.where(dist > rng, -1, oi)
+    assert np.array_equal(idx, want)
+    assert (idx < 0).sum() > 100 and (idx >= 0).sum() > 100
+    assert np.isinf(d2[idx < 0]).all()
+
+
+@pytest.mark.parametrize("cell", [0.0625, 0.25, 1.0, 4.0])
+def test_nn_any_cell_size(scene, pcd, ctx, cell):
+    cl = pcd.Cloud(ctx, scene["world"], direction_trans=False)
+    info = cl.build_index(cell)
+    assert info["cell"] == cell
+    q = scene["q"][:8000]
+    idx, d2 = cl.nn(q)
+    oi, od = scene["tree"].nn(q)
+    assert np.array_equal(idx, oi) and np.array_equal(d2, od)
+    cl.close()
+
+
+def test_nn_edge_cases(scene, pcd, ctx, orc):
+    world = scene["world"]
+    cl = scene["cloud"]
+    # empty batch
+    idx, d2 = cl.nn(np.zeros((0, 3)))
+    assert len(idx) == 0
+    # NaN / inf queries -> no neighbour; far-away queries still find the exact NN when unbounded
+    lo, hi = world[:, :3].min(0), world[:, :3].max(0)
+    q = np.array([[np.nan, 0, 0], [np.inf, 0, 0], [hi[0] + 500.0, 0.3, 1.0], [lo[0] - 80.0, lo[1] - 90.0, lo[2] - 70.0],
+                  [0.5 * (lo[0] + hi[0]), lo[1] - 30.0, 0.5 * (lo[2] + hi[2])]])
+    idx, d2 = cl.nn(q)
+    assert idx[0] == -1 and idx[1] == -1
+    bi, bd = orc.nn_brute(world, q[2:])
+    assert np.array_equal(idx[2:], bi) and np.array_equal(d2[2:], bd)
+    # same far queries with a radius: nothing within 1.5 m
+    idx, _ = cl.nn(q, 1.5)
+    assert (idx == -1).all()
+    # small batch path (no sort) and a batch in the sorted path give identical answers
+    a, _ = cl.nn(scene["q"][:100]); b, _ = cl.nn(scene["q"][:5000])
+    assert np.array_equal(a, b[:100])
+
+
+def test_nn_ties_lowest_index(pcd, ctx, orc):
+    # duplicated and mirrored points: exact float ties must resolve to the lowest index
+    rng = np.random.default_rng(5)
+    base = rng.uniform(-3, 3, (2000, 3)).astype(np.float32)
+    pts = np.concatenate([base, base[::-1], base])            # every location three times
+    cloud = np.zeros((len(pts), 8), np.float32); cloud[:, :3] = pts; cloud[:, 5] = -1.0
+    cl = pcd.Cloud(ctx, cloud); cl.build_index()
+    q = np.concatenate([base[:500].astype(np.float64), rng.uniform(-3, 3, (3000, 3))])
+    idx, d2 = cl.nn(q)
+    bi, bd = orc.nn_brute(cloud, q)
+    assert np.array_equal(idx, bi) and np.array_equal(d2, bd)
+    assert (idx[:500] == np.arange(500)).all()
+    cl.close()
+
+
+def test_nn_tiny_and_degenerate_clouds(pcd, ctx, orc):
+    one = np.zeros((1, 8), np.float32); one[0, :3] = [1, 2, 3]; one[0, 4] = 1
+    cl = pcd.Cloud(ctx, one); cl.build_index()
+    idx, d2 = cl.nn(np.array([[0.0, 0, 0], [100.0, 5, 5]]))
+    assert (idx == 0).all() and d2[0] == np.float32(14.0)
+    cl.close()
+    empty = pcd.Cloud(ctx, np.zeros((0, 8), np.float32)); empty.build_index()
+    idx, _ = empty.nn(np.zeros((3, 3)))
+    assert (idx == -1).all()
+    empty.close()
+    # all points on a line (two grid dimensions collapse to 1)
+    line = np.zeros((5000, 8), np.float32); line[:, 0] = np.linspace(0, 50, 5000); line[:, 5] = 1
+    cl = pcd.Cloud(ctx, line); cl.build_index()
+    q = np.random.default_rng(1).uniform(-5, 55, (3000, 3)) * [1, 0.05, 0.05]
+    idx, d2 = cl.nn(q)
+    bi, bd = orc.nn_brute(line, q)
+    assert np.array_equal(idx, bi) and np.array_equal(d2, bd)
+    cl.close()
+
+
+def test_search_nn_wrapper(scene, orc):
+    # a5: widen + NaN / zero-normal rejection.  The synthetic cloud holds 0.1% zero normals.
+    q = scene["q"][:6000]
+    l, ok = scene["cloud"].search_nn(q)
+    oi, _ = scene["tree"].nn(q)
+    nrm = np.linalg.norm(scene["world"][oi, 4:7].astype(np.float64), axis=1)
+    assert np.array_equal(ok, nrm >= 1e-6)
+    assert np.array_equal(l[:, :3], scene["world"][oi, :3].astype(np.float64))
+    assert np.array_equal(l[:, 3:], scene["world"][oi, 4:7].astype(np.float64))
+    ok1, l1, i1 = scene["tree"].search_nn(q[0])
+    assert ok1 == ok[0] and np.array_equal(l1, l[0])
+
+
+# ---------------------------------------------------------------- association (a6-a8) ------
+@pytest.mark.parametrize("variant", [0, 1, 2])
+def test_associate_matches_reference_loops(scene, orc, variant):
+    rng = orc.search_range(scene["opt_num"])
+    got = scene["cloud"].associate(scene["q"], range_=None if variant == 2 else rng, variant=variant)
+    want = scene["tree"].associate(scene["q"], None if variant == 2 else rng, variant=variant)
+    assert np.array_equal(got["accepted"], want["accepted"])
+    acc = want["accepted"].astype(bool)
+    assert 0.3 < acc.mean() < 0.999
+    assert np.array_equal(got["idx"][acc], want["idx"][acc])
+    assert np.array_equal(got["type"][acc], want["type"][acc])
+    assert np.array_equal(got["rgb"][acc], want["rgb"][acc])
+    assert set(np.unique(want["type"][acc])) == {1, 2}
+    for f in ("xyz", "abcd", "dist", "angle"):
+        assert _close(got[f][acc], want[f][acc]), f
+    # in practice the fp64 fields are bit-identical (same operation order, no FMA)
+    assert np.array_equal(got["abcd"][acc], want["abcd"][acc])
+
+
+def test_associate_opt_num_sweep_equals_explicit_range(scene, orc):
+    a = scene["cloud"].associate(scene["q"][:20000], opt_num=scene["opt_num"][:20000], sweep=(1.5, 0.2, 0.1), variant=1)
+    b = scene["cloud"].associate(scene["q"][:20000], range_=orc.search_range(scene["opt_num"][:20000]), variant=1)
+    for f in a:
+        assert np.array_equal(a[f], b[f], equal_nan=True) if a[f].dtype.kind == "f" else np.array_equal(a[f], b[f])
+
+
+def test_associate_multi_chunk_pipeline(scene, orc, pcd, ctx):
+    # > 2^20 queries exercises the double-buffered H2D / compute / D2H pipeline
+    rng = np.random.default_rng(3)
+    sel = rng.integers(0, len(scene["q"]), 2_300_000)
+    q = scene["q"][sel] + rng.normal(0, 0.02, (len(sel), 3))
+    got = scene["cloud"].associate(q, range_=0.6, variant=0, fields=("idx", "accepted", "abcd"))
+    want = scene["tree"].associate(q, 0.6, variant=0)
+    assert np.array_equal(got["accepted"], want["accepted"])
+    acc = want["accepted"].astype(bool)
+    assert np.array_equal(got["idx"][acc], want["idx"][acc])
+    assert np.array_equal(got["abcd"][acc], want["abcd"][acc])
+
+
+def test_match_proj(ctx, orc):
+    rng = np.random.default_rng(11)
+    n = 3000
+    counts = rng.integers(0, 5, n); cs = np.concatenate([[0], np.cumsum(counts)])
+    p = rng.normal(0, 3, (n, 3))
+    cand = np.concatenate([rng.normal(0, 3, (cs[-1], 3)), rng.normal(0, 1, (cs[-1], 3))], 1)
+    found, xyz, abcd, dist, ang = ctx.match_proj(p, cand, cs)
+    for i in range(n):
+        ok, x, a, d, g = orc.match_proj(p[i], cand[cs[i]:cs[i + 1]])
+        assert ok == bool(found[i])
+        if ok:
+            assert _close(xyz[i], x) and _close(abcd[i], a) and _close(dist[i], d) and _close(ang[i], g)
+
+
+# ---------------------------------------------------------------- cost function (a18-a19) --
+def test_residual_jacobian(scene, ctx, orc):
+    rec = scene["tree"].associate(scene["q"], 1.5, variant=0)
+    acc = rec["accepted"].astype(bool)
+    p, abcd = scene["q"][acc], rec["abcd"][acc]
+    w = ctx.weights_from_type(rec["type"][acc], 10.0, 1000.0, 10000.0)
+    assert set(np.unique(w)) == {1000.0, 10000.0}
+    r, J, s = ctx.residual_jacobian(p, abcd, w)
+    ro, Jo = orc.resjac(p, abcd, w)
+    assert _close(r, ro) and _close(J, Jo)
+    assert np.array_equal(r, ro) and np.array_equal(J, Jo)       # bit-identical in practice
+    assert abs(s - float(np.sum(ro * ro))) <= 1e-9 * s
+    # closed form: J = w * sign(n.p + d) * n
+    sgn = np.sign((p * abcd[:, :3]).sum(1) + abcd[:, 3])
+    assert np.allclose(J, (w * sgn)[:, None] * abcd[:, :3], rtol=1e-12, atol=0)
+    # run-to-run determinism of the reduction
+    assert ctx.residual_jacobian(p, abcd, w)[2] == s
+
+
+def test_residual_jacobian_nan_at_zero_and_fd(ctx, orc):
+    abcd = np.array([[0.0, -1.0, 0.0, 1.6], [0.6, 0.0, 0.8, -2.0]])
+    p = np.array([[3.0, 1.6, 4.0], [1.0, 5.0, 1.0]])     # first point lies exactly on its plane
+    w = np.array([1000.0, 10.0])
+    r, J, _ = ctx.residual_jacobian(p, abcd, w)
+    ro, Jo = orc.resjac(p, abcd, w)
+    assert r[0] == 0.0 and np.isnan(J[0]).all() and np.isnan(Jo[0]).all()     # F12: 0 * inf
+    assert _close(r, ro) and _close(J, Jo)
+    eps = 1e-6
+    for k in range(3):
+        dp = p.copy(); dp[1, k] += eps
+        fd = (ctx.residual_jacobian(dp, abcd, w)[0][1] - r[1]) / eps
+        assert abs(fd - J[1, k]) < 1e-4 * max(1.0, abs(J[1, k]))
+
+
+def test_pose_jacobian_extension_fd(ctx):
+    # north_star extension, no reference counterpart: checked against finite differences only
+    rng = np.random.default_rng(2)
+    n = 50
+    q = rng.normal(0, 1, (n, 4)); q /= np.linalg.norm(q, axis=1, keepdims=True)
+    t = rng.normal(0, 2, (n, 3)); pc = rng.normal(0, 5, (n, 3))
+    nn = rng.normal(0, 1, (n, 3)); nn /= np.linalg.norm(nn, axis=1, keepdims=True)
+    abcd = np.concatenate([nn, rng.normal(0, 1, (n, 1))], 1); w = np.full(n, 100.0)
+    r, Jp, Jq = ctx.residual_pose_jacobian(pc, q, t, abcd, w)
+    eps = 1e-7
+    for k in range(7):
+        q2, t2 = q.copy(), t.copy()
+        if k < 4: q2[:, k] += eps
+        else: t2[:, k - 4] += eps
+        r2, _, _ = ctx.residual_pose_jacobian(pc, q2, t2, abcd, w)
+        fd = (r2 - r) / eps
+        assert np.allclose(fd, Jq[:, k], rtol=2e-4, atol=2e-3), k
+
+
+def test_filter_outliers(scene, ctx, orc):
+    rec = scene["tree"].associate(scene["q"][:10000], 1.5, variant=0)
+    typ = rec["type"].copy(); typ[::7] = 0
+    e, cnt = ctx.filter_outliers(scene["q"][:10000], rec["xyz"], typ, 0.05, 0.12)
+    eo, co = orc.filter_outliers(scene["q"][:10000], rec["xyz"], typ, 0.05, 0.12)
+    assert np.array_equal(e, eo) and cnt == co and 0 < cnt < 10000
+
+
+# ---------------------------------------------------------------- depth projection (a9-a15) -
+@pytest.fixture(scope="module")
+def proj_scene(scene, orc, synth, pcd):
+    opt_g, opt_o = pcd.ProjOptions.default(), orc.ProjOptions.default()
+    n_cells = scene["cloud"].build_submap(opt_g)
+    sub = orc.Submap(scene["world"], opt_o)
+    assert n_cells == sub.n_cells
+    cams = synth.make_cameras(6, scene["info"])
+    coef = orc.splat_coef(cams[0]["cam"], opt_o)
+    assert np.array_equal(coef, pcd.splat_coef(cams[0]["cam"], opt_g))
+    return dict(sub=sub, cams=cams, coef=coef, opt_g=opt_g, opt_o=opt_o)
+
+
+def _winners(z, px):
+    idx = np.full(len(px), -1, np.int32); rng = np.full(len(px), np.inf, np.float32)
+    ok = px >= 0
+    v = z.ravel()[px[ok]]
+    hit = v != np.iinfo(np.uint64).max
+    ii = np.where(hit, (v & np.uint64(0xffffffff)).astype(np.int64), -1).astype(np.int32)
+    rr = np.where(hit, (v >> np.uint64(32)).astype(np.uint32).view(np.float32), np.inf).astype(np.float32)
+    idx[ok] = ii; rng[ok] = rr
+    return idx, rng
+
+
+def test_zbuffer_dense_bit_exact(scene, proj_scene, pcd):
+    ps = proj_scene
+    for cam in ps["cams"][:3]:
+        im = pcd.Image.make(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"])
+        _, _, z, stats = scene["cloud"].project_image(im, ps["coef"], None, dense=True)
+        zo, counters, n_sel = ps["sub"].project(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"], ps["coef"])
+        assert stats[0] == n_sel and stats[1] == counters[0] and stats[2] == counters[1]
+        assert counters[0] > 1000
+        assert np.array_equal(z, zo)
+        assert (z != np.iinfo(np.uint64).max).mean() > 0.05
+
+
+def test_zbuffer_feature_winners_bit_exact(scene, proj_scene, pcd, orc, synth):
+    ps = proj_scene
+    feats = synth.make_features(3000)
+    for cam in ps["cams"]:
+        im = pcd.Image.make(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"])
+        widx, wr, _, stats = scene["cloud"].project_image(im, ps["coef"], feats)
+        px = orc.feature_pixels(feats, 0.2, cam["width"], cam["height"])
+        s = 0.2; ih, iw = int(cam["height"] * s), int(cam["width"] * s)
+        mask = np.zeros(ih * iw, np.uint8); mask[px[px >= 0]] = 1
+        zo, _, _ = ps["sub"].project(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"], ps["coef"], mask)
+        oi, orng = _winners(zo, px)
+        assert np.array_equal(widx, oi)
+        assert np.array_equal(wr.view(np.uint32), orng.view(np.uint32))
+        assert (widx >= 0).sum() > 200 and stats[3] == (widx >= 0).sum()
+        # a15 ray/plane on the winners
+        m, xyz = scene["cloud"].ray_plane(im, feats, widx)
+        assert np.array_equal(m, widx >= 0)
+        for k in np.flatnonzero(m)[:50]:
+            assert _close(xyz[k], orc.ray_plane(scene["world"], int(widx[k]), cam["cam"], feats[k, 0], feats[k, 1]))
+
+
+def test_project_images_batch_equals_single(scene, proj_scene, pcd, synth):
+    ps = proj_scene
+    feats = [synth.make_features(500 + 100 * k, seed=100 + k) for k in range(len(ps["cams"]))]
+    ims = [pcd.Image.make(c["qvec"], c["tvec"], c["cam"], c["width"], c["height"]) for c in ps["cams"]]
+    fs = np.concatenate([[0], np.cumsum([len(f) for f in feats])])
+    widx, wr, stats = scene["cloud"].project_images(ims, ps["coef"], np.concatenate(feats), fs)
+    for k, im in enumerate(ims):
+        a, b, _, _ = scene["cloud"].project_image(im, ps["coef"], feats[k])
+        assert np.array_equal(widx[fs[k]:fs[k + 1]], a) and np.array_equal(wr[fs[k]:fs[k + 1]], b)
+
+
+def test_zbuffer_full_res_and_empty_frustum(scene, orc, synth, pcd, ctx):
+    # depth_image_scale = 1 at 1920x1080 (config 4 shape), plus a camera looking away from everything
+    opt_g = pcd.ProjOptions.default(depth_image_scale=1.0); opt_o = orc.ProjOptions.default(depth_image_scale=1.0)
+    cl = pcd.Cloud(ctx, scene["world"]); cl.build_submap(opt_g)
+    sub = orc.Submap(scene["world"], opt_o)
+    cams = synth.make_cameras(2, scene["info"], cam=synth.OPENCV_1080)
+    coef = orc.splat_coef(cams[0]["cam"], opt_o)
+    cam = cams[1]
+    im = pcd.Image.make(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"])
+    _, _, z, stats = cl.project_image(im, coef, None, dense=True)
+    zo, counters, n_sel = sub.project(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"], coef)
+    assert z.shape == (1080, 1920) and np.array_equal(z, zo) and stats[2] == counters[1]
+    far = pcd.Image.make([1, 0, 0, 0], [0, 0, 5000.0], cam["cam"], cam["width"], cam["height"])
+    widx, _, z, stats = cl.project_image(far, coef, synth.make_features(100, cam=synth.OPENCV_1080), dense=True)
+    assert stats[0] == 0 and (widx == -1).all() and (z == np.iinfo(np.uint64).max).all()
+    cl.close()
