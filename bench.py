@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""bench.py -- association queries/s and residual+Jacobian evals/s of the src/lidar path on B200.
+
+  python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run)
+  python bench.py --impl reference --gpus N --steps K --warmup W
+
+A "step" is one pass of the hot path over one batch of synthetic SfM points: the association
+pass (query keys + sort + grid 1-NN + LidarPoint record, reference loops at
+src/sfm/incremental_mapper.cc:1413-1469) followed by the cost-function pass (weight by type +
+residual + 1x3 Jacobian + sum r^2, src/base/cost_functions.h:204-232).  The cloud and its index
+are replicated on every GPU, the queries are sharded (weak scaling: Q per GPU is fixed), and
+the only exchange is an all-reduce of sum r^2 and the accepted counters.
+
+Workload (BASELINE.json configs[4]): queries against a 50 M-point cloud, the configuration the
+metric "at 1/2/4/8 B200" is quoted on.  --workload smith runs configs[1] (1 M cloud, 50 k points).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as entry  # noqa: E402
+
+ALG_BYTES_NN = 260.0       # 12 B query + 8 B result + one 15-point leaf x 16 B
+ALG_BYTES_RECORD = 56.0
+ALG_BYTES_RESJAC = 96.0
+WEIGHTS = (10.0, 1000.0, 10000.0)          # proj / icp / icp_ground (src/controllers/incremental_mapper.h:74-78)
+SWEEP = (1.5, 0.2, 0.1)                    # kdtree max / min search range, drop speed (:64-66)
+
+WORKLOADS = {
+    # name: (cloud points, queries per GPU, description)
+    "sweep50m": (50_000_000, 16_000_000, "configs[4]: association queries vs 50M-pt cloud, queries sharded, cloud replicated"),
+    "full10m": (10_000_000, 1_000_000, "configs[2]: 10M-pt cloud, 1M SfM points"),
+    "smith": (1_000_000, 50_000, "configs[1]: Smith-Hall-shaped scene, 1M-pt cloud, 50k SfM points"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="sweep50m", choices=sorted(WORKLOADS))
+    ap.add_argument("--cloud", type=int, default=0, help="override cloud size")
+    ap.add_argument("--queries", type=int, default=0, help="override queries per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work of the cpu_baseline sample")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def load_mods():
+    pcd = entry.package()
+    synth = entry._load("pcd_synth", os.path.join(entry.PKG, "synth.py"))
+    return pcd, synth
+
+
+def load_oracle():
+    """The CPU checker / baseline.  bench.py may execute it ONLY for cpu_baseline and --impl reference."""
+    return entry._load("orc", os.path.join(ROOT, "oracle", "orc.py"))
+
+
+def workload_sizes(args):
+    n_cloud, q, desc = WORKLOADS[args.workload]
+    if args.cloud:
+        n_cloud = args.cloud
+    if args.queries:
+        q = args.queries
+    return n_cloud, q, desc
+
+
+def base_line(args, n_cloud, q_per_gpu, desc, world):
+    return {"metric": "ICP association queries/s (NN + LidarPoint record + residual/Jacobian pass)", "unit": "queries/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 NN distance / f64 record, residual, Jacobian", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {desc}", "cloud_points": n_cloud, "queries_per_gpu": q_per_gpu,
+                       "queries_total": q_per_gpu * world, "radius_sweep": list(SWEEP), "variant": "global (incremental_mapper.cc:1430-1468)",
+                       "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
+                       "parallelism": f"queries sharded x{world}, cloud+index replicated"}}
+
+
+def cpu_pass(orc, tree, q, rng, threads):
+    """One reference-restated CPU step on a sample: association loop + weights + residual/Jacobian."""
+    t0 = time.perf_counter()
+    rec = tree.associate(q, rng, variant=1, threads=threads)
+    t1 = time.perf_counter()
+    w = np.where(rec["type"] == 1, WEIGHTS[1], np.where(rec["type"] == 2, WEIGHTS[2], 0.0))
+    r, J = orc.resjac(q, rec["abcd"], w, threads=threads)
+    t2 = time.perf_counter()
+    return t1 - t0, t2 - t1, rec, r
+
+
+def pick_threads(orc, tree, q, rng):
+    """All host threads unless a probe shows fewer are faster (cgroup-limited boxes oversubscribe)."""
+    best, best_t = 1, None
+    cand = sorted({1, max(1, orc.max_threads() // 2), orc.max_threads()})
+    for th in cand:
+        cpu_pass(orc, tree, q[:20_000], rng[:20_000], th)
+        ta, tr, _, _ = cpu_pass(orc, tree, q, rng, th)
+        if best_t is None or ta + tr < best_t:
+            best, best_t = th, ta + tr
+    return best
+
+
+def cpu_baseline(orc, world_cloud, q, opt_num, seconds):
+    """Reference-restated CPU path on a bounded sample of the same workload, all host threads."""
+    t0 = time.perf_counter()
+    tree = orc.KdTree(world_cloud)
+    build_s = time.perf_counter() - t0
+    rng = orc.search_range(opt_num, *SWEEP)
+    probe = min(len(q), 100_000)
+    threads = pick_threads(orc, tree, q[:probe], rng[:probe])
+    ta, tr, _, _ = cpu_pass(orc, tree, q[:probe], rng[:probe], threads)
+    per_q = (ta + tr) / probe
+    m = int(min(len(q), max(probe, seconds / max(per_q, 1e-12))))
+    ta, tr, rec, _ = cpu_pass(orc, tree, q[:m], rng[:m], threads)
+    return {"value": m / (ta + tr), "unit": "queries/s", "cores": threads, "kind": "port",
+            "sample": f"{m} of the step's queries against the full cloud (association {ta:.2f} s + residual/Jacobian {tr:.2f} s); "
+                      f"kd-tree build {build_s:.1f} s not included",
+            "assoc_queries_per_s": m / ta, "resjac_evals_per_s": m / tr, "accepted_frac": float(rec["accepted"].mean())}, tree
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port: PCL/FLANN/Eigen/Ceres are absent, so the
+    reference itself cannot be compiled here) on the host cores, same config / metric / unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pcd, synth = load_mods()
+    orc = load_oracle()
+    n_cloud, q_per_gpu, desc = workload_sizes(args)
+    raw, _ = synth.make_cloud(n_cloud, seed=synth.SEED0 + 4)
+    world_cloud = orc.direction_trans(raw)
+    del raw
+    tree = orc.KdTree(world_cloud)
+    # bounded sample per step: sized from a probe so that the whole run ends within a few minutes
+    qp, onp = synth.make_queries(world_cloud, 100_000, seed=synth.SEED0 + 100)
+    rngp = orc.search_range(onp, *SWEEP)
+    threads = pick_threads(orc, tree, qp, rngp)
+    ta, tr, _, _ = cpu_pass(orc, tree, qp, rngp, threads)
+    budget = 120.0 / max(1, args.steps + args.warmup)
+    m = int(min(q_per_gpu, max(100_000, budget / ((ta + tr) / len(qp)))))
+    q, on = synth.make_queries(world_cloud, m, seed=synth.SEED0 + 100)
+    rng = orc.search_range(on, *SWEEP)
+    for _ in range(args.warmup):
+        cpu_pass(orc, tree, q, rng, threads)
+    t0 = time.perf_counter()
+    ta_sum = tr_sum = 0.0
+    for _ in range(args.steps):
+        ta, tr, _, _ = cpu_pass(orc, tree, q, rng, threads)
+        ta_sum += ta; tr_sum += tr
+    dt = time.perf_counter() - t0
+    value = m * args.steps / dt
+    line = base_line(args, n_cloud, q_per_gpu, desc, args.gpus)
+    line.update({"impl": "reference", "value": value, "ms_per_step": 1e3 * dt / args.steps, "gpu_launches": 0,
+                 "cpu_baseline": {"value": value, "unit": "queries/s", "cores": threads, "kind": "port",
+                                  "sample": f"{m} queries per step against the full {len(world_cloud)}-point cloud"},
+                 "assoc_queries_per_s": m * args.steps / ta_sum, "resjac_evals_per_s": m * args.steps / tr_sum,
+                 "e2e": {"value": value, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pcd, synth = load_mods()
+    n_cloud, Q, desc = workload_sizes(args)
+    ctx = pcd.Context(local)
+    dev = torch.device("cuda", local)
+
+    # ---- cloud: generated on rank 0, replicated over NCCL/NVLink, indexed on every GPU -------------
+    t_gen = time.perf_counter()
+    if rank == 0:
+        raw, _ = synth.make_cloud(n_cloud, seed=synth.SEED0 + 4)
+        d_raw = torch.from_numpy(raw).to(dev)
+        del raw
+    else:
+        d_raw = torch.empty((n_cloud, 8), dtype=torch.float32, device=dev)
+    if world > 1:
+        dist.broadcast(d_raw, src=0)
+    torch.cuda.synchronize()
+    t_gen = time.perf_counter() - t_gen
+    t_build = time.perf_counter()
+    cloud = pcd.Cloud(ctx, device_ptr=d_raw.data_ptr(), n=n_cloud, direction_trans=True)
+    del d_raw
+    info = cloud.build_index()
+    t_build = time.perf_counter() - t_build
+    world_cloud = cloud.download()          # host copy: query synthesis (and the CPU baseline on rank 0)
+
+    # ---- this rank's shard of the SfM points (hash order), pinned for the end-to-end leg ------------
+    q_np, on_np = synth.make_queries(world_cloud, Q, seed=synth.SEED0 + 100 + rank)
+    h_q = pcd.pinned_empty((Q, 3), np.float64); h_q[:] = q_np
+    h_on = pcd.pinned_empty((Q,), np.int32); h_on[:] = on_np
+    if rank != 0:
+        del world_cloud
+    d_q = torch.from_numpy(q_np).to(dev)
+    d_on = torch.from_numpy(on_np).to(dev)
+    o = {"idx": torch.empty(Q, dtype=torch.int32, device=dev), "accepted": torch.empty(Q, dtype=torch.uint8, device=dev),
+         "type": torch.empty(Q, dtype=torch.uint8, device=dev), "rgb": torch.empty((Q, 3), dtype=torch.uint8, device=dev),
+         "xyz": torch.empty((Q, 3), dtype=torch.float64, device=dev), "abcd": torch.empty((Q, 4), dtype=torch.float64, device=dev),
+         "dist": torch.empty(Q, dtype=torch.float64, device=dev), "angle": torch.empty(Q, dtype=torch.float64, device=dev)}
+    optrs = {k: v.data_ptr() for k, v in o.items()}
+    d_w = torch.empty(Q, dtype=torch.float64, device=dev)
+    d_r = torch.empty(Q, dtype=torch.float64, device=dev)
+    d_J = torch.empty((Q, 3), dtype=torch.float64, device=dev)
+    d_sum = torch.zeros(3, dtype=torch.float64, device=dev)
+    flush = None if Q * 24 > 126e6 * 2 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        cloud.associate_dev(d_q.data_ptr(), 0, d_on.data_ptr(), SWEEP, Q, pcd.ASSOC_GLOBAL, optrs, stream)
+        ctx.weights_from_type_dev(o["type"].data_ptr(), Q, *WEIGHTS, d_w.data_ptr(), stream)
+        ctx.residual_jacobian_dev(d_q.data_ptr(), o["abcd"].data_ptr(), d_w.data_ptr(), Q, d_r.data_ptr(), d_J.data_ptr(),
+                                  d_sum.data_ptr(), stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+        if flush is not None:
+            flush.fill_(1)
+    barrier()
+    ctx.profile(True)
+    launches0 = ctx.launches
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for a, b in evs:
+        a.record()
+        step()
+        b.record()
+        if flush is not None:
+            flush.fill_(1)
+    barrier()
+    gpu_ms = sum(a.elapsed_time(b) for a, b in evs)
+    launches = ctx.launches - launches0
+    ktime = {k: ctx.kernel_time(getattr(pcd, k)) for k in ("K_NN_KEYSORT", "K_NN_SEARCH", "K_ASSOC_RECORD", "K_RESJAC")}
+    ctx.profile(False)
+    accepted = int(o["accepted"].sum().item())
+    # the path's one exchange: sum r^2 and counters over ranks (r is NaN-free: w = 0 rows give r = 0)
+    red = torch.tensor([gpu_ms, float(accepted), float(torch.nansum(d_r * d_r).item())], dtype=torch.float64, device=dev)
+    mx = red.clone()
+    if world > 1:
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(red, op=dist.ReduceOp.SUM)
+    gpu_ms_max = float(mx[0].item())
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end to end: the host-pointer C ABI, pinned host buffers, H2D + D2H inside the timed region ----
+    fields = ("idx", "accepted", "type", "xyz", "abcd", "dist")
+    shapes = {"idx": ((Q,), np.int32), "accepted": ((Q,), np.uint8), "type": ((Q,), np.uint8), "xyz": ((Q, 3), np.float64),
+              "abcd": ((Q, 4), np.float64), "dist": ((Q,), np.float64)}
+    h_out = {f: pcd.pinned_empty(*shapes[f]) for f in fields}
+    h_w = pcd.pinned_empty((Q,), np.float64)
+    h_r = pcd.pinned_empty((Q,), np.float64)
+    h_J = pcd.pinned_empty((Q, 3), np.float64)
+
+    def e2e_step():
+        cloud.associate(h_q, opt_num=h_on, sweep=SWEEP, variant=pcd.ASSOC_GLOBAL, fields=fields, out=h_out)
+        ctx.weights_from_type(h_out["type"], *WEIGHTS, out=h_w)
+        return ctx.residual_jacobian(h_q, h_out["abcd"], h_w, out=(h_r, h_J))[2]
+
+    e2e_steps = max(2, min(args.steps, 5))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+    h2d = Q * (24 + 4) + Q * 1 + Q * (24 + 32 + 8)
+    d2h = sum(int(np.prod(shapes[f][0])) * np.dtype(shapes[f][1]).itemsize for f in fields) + Q * 8 + Q * (8 + 24) + 8
+
+    if rank == 0:
+        ms_step = gpu_ms_max / args.steps
+        line = base_line(args, n_cloud, Q, desc, world)
+        peak, peak_src = measured_peak()
+        nn_ms, nn_n = ktime["K_NN_SEARCH"]
+        nn_avg_s = 1e-3 * nn_ms / max(nn_n, 1)
+        achieved = ALG_BYTES_NN * Q / nn_avg_s / 1e9
+        line.update({"value": Q * world / (ms_step * 1e-3), "ms_per_step": ms_step, "gpu_launches": int(launches),
+                     "clocks": clocks,
+                     "e2e": {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
+                             "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                             "api": "pcd_associate_batch + pcd_weights_from_type + pcd_residual_jacobian_batch (host pointers, pinned)"},
+                     "roofline": {"bound": "hbm", "kernel": "k_nn_search", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                                  "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                                  "algorithmic_bytes_per_query": ALG_BYTES_NN, "queries_per_launch": Q,
+                                  "avg_launch_ms": 1e3 * nn_avg_s, "launches_timed": int(nn_n)},
+                     "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktime.items()},
+                     "assoc_queries_per_s_per_gpu": Q / (1e-3 * (ktime["K_NN_KEYSORT"][0] + ktime["K_NN_SEARCH"][0] + ktime["K_ASSOC_RECORD"][0]) / args.steps),
+                     "resjac_evals_per_s_per_gpu": Q / (1e-3 * ktime["K_RESJAC"][0] / args.steps),
+                     "resjac_roofline_frac": ALG_BYTES_RESJAC * Q / (1e-3 * ktime["K_RESJAC"][0] / max(ktime["K_RESJAC"][1], 1)) / 1e9 / peak,
+                     "accepted_frac": float(red[1].item()) / (Q * world), "sum_sq": float(red[2].item()),
+                     "index": info, "setup_s": {"cloud_gen_and_replicate": t_gen, "upload_and_index_build": t_build}})
+        if world == 1 and not args.no_cpu_baseline:
+            orc = load_oracle()
+            cb, _ = cpu_baseline(orc, world_cloud, q_np, on_np, args.cpu_seconds)
+            line["cpu_baseline"] = cb
+        print(json.dumps(line), flush=True)
+    cloud.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

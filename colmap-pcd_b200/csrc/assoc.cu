@@ -158,6 +158,7 @@ int pcd_associate_batch_dev(pcd_cloud* cloud, const double* d_p, const double* d
   if (rc) return rc;
   pcd_range_sweep sw = sweep ? *sweep : pcd_range_sweep{0, 0, 0};
   pcd_assoc_out o = *d_out; o.idx = nullptr;   // idx already written by the search (or private)
+  pcd::ProfScope ps(ctx, PCD_K_ASSOC_RECORD, st);
   pcd::k_assoc_record<<<pcd_blocks(n, 256), 256, 0, st>>>((const float4*)cloud->aos, d_p, d_idx, rr, on, sw, n, variant, o, nullptr);
   PCD_LAUNCH_CHECK(ctx);
   return PCD_OK;

@@ -79,7 +79,35 @@ struct pcd_ctx {
   pcd::DevBuf stage_in[2], stage_out[2], stage_aux[2];
   pcd::PinBuf pin_in[2], pin_out[2];
   pcd::DevBuf img_buf, feat_buf, zbuf, sel_buf;
+  // optional per-kernel CUDA-event timing (pcd_ctx_profile); spans are resolved lazily
+  bool prof = false;
+  struct Span { cudaEvent_t a, b; int which; };
+  std::vector<Span> prof_pending;
+  std::vector<cudaEvent_t> prof_free;
+  double prof_ms[PCD_K_COUNT] = {};
+  int64_t prof_n[PCD_K_COUNT] = {};
 };
+
+namespace pcd {
+// Brackets the launches of one kernel class with CUDA events on the launching stream.
+struct ProfScope {
+  pcd_ctx* c; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr; int which;
+  static cudaEvent_t get(pcd_ctx* c) {
+    if (!c->prof_free.empty()) { cudaEvent_t e = c->prof_free.back(); c->prof_free.pop_back(); return e; }
+    cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+  }
+  ProfScope(pcd_ctx* c_, int which_, cudaStream_t st_) : c(c_), st(st_), which(which_) {
+    if (!c->prof) return;
+    a = get(c); b = get(c);
+    cudaEventRecord(a, st);
+  }
+  ~ProfScope() {
+    if (!a) return;
+    cudaEventRecord(b, st);
+    c->prof_pending.push_back({a, b, which});
+  }
+};
+}  // namespace pcd
 
 struct pcd_cloud {
   pcd_ctx* ctx = nullptr;

@@ -46,6 +46,8 @@ void pcd_ctx_destroy(pcd_ctx* c) {
   for (auto* b : bufs) b->release();
   for (int i = 0; i < 2; i++) { c->pin_in[i].release(); c->pin_out[i].release(); }
   for (int i = 0; i < 8; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  for (auto& s : c->prof_pending) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+  for (auto e : c->prof_free) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
   if (c->copy_in) cudaStreamDestroy(c->copy_in);
   if (c->copy_out) cudaStreamDestroy(c->copy_out);
@@ -67,6 +69,32 @@ int pcd_ctx_counters(const pcd_ctx* c, int64_t out[4]) {
 }
 
 int64_t pcd_ctx_launches(const pcd_ctx* c) { return c ? c->launches : 0; }
+
+int pcd_ctx_profile(pcd_ctx* c, int enable) {
+  if (!c) return PCD_E_INVALID;
+  DeviceGuard g(c->device);
+  for (auto& s : c->prof_pending) { cudaEventSynchronize(s.b); c->prof_free.push_back(s.a); c->prof_free.push_back(s.b); }
+  c->prof_pending.clear();
+  for (int i = 0; i < PCD_K_COUNT; i++) { c->prof_ms[i] = 0.0; c->prof_n[i] = 0; }
+  c->prof = enable != 0;
+  return PCD_OK;
+}
+
+int pcd_ctx_kernel_time(pcd_ctx* c, int which, double* total_ms, int64_t* launches) {
+  if (!c || which < 0 || which >= PCD_K_COUNT) return PCD_E_INVALID;
+  DeviceGuard g(c->device);
+  for (auto& s : c->prof_pending) {
+    PCD_CUDA(c, cudaEventSynchronize(s.b));
+    float ms = 0.0f;
+    PCD_CUDA(c, cudaEventElapsedTime(&ms, s.a, s.b));
+    c->prof_ms[s.which] += ms; c->prof_n[s.which]++;
+    c->prof_free.push_back(s.a); c->prof_free.push_back(s.b);
+  }
+  c->prof_pending.clear();
+  if (total_ms) *total_ms = c->prof_ms[which];
+  if (launches) *launches = c->prof_n[which];
+  return PCD_OK;
+}
 
 int pcd_host_alloc(void** out, int64_t bytes) {
   if (!out || bytes < 0) return PCD_E_INVALID;

@@ -313,6 +313,7 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   static int group = [] { const char* e = getenv("PCD_B200_NN_GROUP"); return e ? atoi(e) : 0; }();
   int G = group ? group : g_nn_group;
   if (n > 2048) {
+    ProfScope ps(ctx, PCD_K_NN_KEYSORT, st);
     PCD_CUDA(ctx, ctx->keys.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->keys_alt.ensure(4 * (size_t)n));
     PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->vals_alt.ensure(4 * (size_t)n));
     cub::DoubleBuffer<uint32_t> kb(ctx->keys.as<uint32_t>(), ctx->keys_alt.as<uint32_t>());
@@ -336,6 +337,7 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   if (chunk > NN_MAX_CHUNK) chunk = NN_MAX_CHUNK;
   int blocks = (int)((n + chunk - 1) / chunk);
   const float4* aos = (const float4*)cloud->aos;
+  ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
   switch (G) {
     case 4: launch_nn<4>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
     case 16: launch_nn<16>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;

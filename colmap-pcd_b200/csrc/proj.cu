@@ -253,6 +253,7 @@ static int project_one(pcd_cloud* c, const pcd_image* img, const double coef[4],
     int64_t warps = c->sub_cells;
     int blocks = (int)((warps + 7) / 8);
     int cap = ctx->sm_count * 16; if (blocks > cap) blocks = cap;
+    ProfScope ps(ctx, PCD_K_PROJECT, st);
     if (dense) k_project<true><<<blocks, 256, 0, st>>>(sm, P, mask, zb, d_stats);
     else k_project<false><<<blocks, 256, 0, st>>>(sm, P, mask, zb, d_stats);
     PCD_LAUNCH_CHECK(ctx);

@@ -133,6 +133,7 @@ int pcd_residual_jacobian_batch_dev(pcd_ctx* ctx, const double* d_p, const doubl
   int nb = pcd_blocks(n, pcd::RJ_THREADS);
   double* partial = nullptr;
   if (d_sum_sq) { PCD_CUDA(ctx, ctx->partial.ensure(8 * (size_t)nb)); partial = ctx->partial.as<double>(); }
+  pcd::ProfScope ps(ctx, PCD_K_RESJAC, st);
   pcd::k_resjac<<<nb, pcd::RJ_THREADS, 0, st>>>(d_p, (const double4*)d_abcd, d_w, n, d_r, d_J, partial);
   PCD_LAUNCH_CHECK(ctx);
   if (d_sum_sq) { pcd::k_sum_partials<<<1, 256, 0, st>>>(partial, nb, d_sum_sq); PCD_LAUNCH_CHECK(ctx); }
@@ -184,6 +185,16 @@ int pcd_residual_pose_jacobian_batch(pcd_ctx* ctx, const double* p_cam, const do
   if (J_point) PCD_CUDA(ctx, cudaMemcpyAsync(J_point, d_Jp, 24 * (size_t)n, cudaMemcpyDeviceToHost, st));
   if (J_pose) PCD_CUDA(ctx, cudaMemcpyAsync(J_pose, d_Jq, 56 * (size_t)n, cudaMemcpyDeviceToHost, st));
   PCD_CUDA(ctx, cudaStreamSynchronize(st));
+  return PCD_OK;
+}
+
+int pcd_weights_from_type_dev(pcd_ctx* ctx, const uint8_t* d_type, int64_t n, double w_proj, double w_icp, double w_ground,
+                              double* d_w_out, void* stream) {
+  if (!ctx || n < 0 || (n > 0 && (!d_type || !d_w_out))) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_weights_from_type_dev: bad argument");
+  if (n == 0) return PCD_OK;
+  DeviceGuard g(ctx->device);
+  pcd::k_weights<<<pcd_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(d_type, n, w_proj, w_icp, w_ground, d_w_out);
+  PCD_LAUNCH_CHECK(ctx);
   return PCD_OK;
 }
 

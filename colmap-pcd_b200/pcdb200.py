@@ -6,11 +6,13 @@ missing -- there is no CPU fallback anywhere on the product path.
 """
 import ctypes as C
 import os
+import weakref
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpcd_b200.so")
 
+K_NN_KEYSORT, K_NN_SEARCH, K_ASSOC_RECORD, K_RESJAC, K_PROJECT = 0, 1, 2, 3, 4
 TYPE_PROJ, TYPE_ICP, TYPE_ICP_GROUND, TYPE_NONE = 0, 1, 2, 255
 ASSOC_LOCAL, ASSOC_GLOBAL, ASSOC_WHOLE_MAP = 0, 1, 2
 
@@ -114,11 +116,28 @@ class Context:
             lib().pcd_ctx_destroy(self._h)
             self._h = C.c_void_p()
 
+    def profile(self, enable=True):
+        self.check(lib().pcd_ctx_profile(self._h, C.c_int(int(enable))), "pcd_ctx_profile")
+
+    def kernel_time(self, which):
+        """(total milliseconds, launches) of kernel class `which` (K_*) since profile(True)."""
+        ms = C.c_double(); n = C.c_int64()
+        self.check(lib().pcd_ctx_kernel_time(self._h, C.c_int(which), C.byref(ms), C.byref(n)), "pcd_ctx_kernel_time")
+        return ms.value, n.value
+
+    def weights_from_type_dev(self, d_type, n, w_proj, w_icp, w_ground, d_w, stream=0):
+        self.check(lib().pcd_weights_from_type_dev(self._h, C.c_void_p(d_type), C.c_int64(n), C.c_double(w_proj),
+                                                   C.c_double(w_icp), C.c_double(w_ground), C.c_void_p(d_w),
+                                                   C.c_void_p(stream)), "pcd_weights_from_type_dev")
+
     # -- a19 --------------------------------------------------------------------------------
-    def residual_jacobian(self, p, abcd, w, jac=True, want_sum=True):
+    def residual_jacobian(self, p, abcd, w, jac=True, want_sum=True, out=None):
         p, abcd, w = _f64(p, 3), _f64(abcd, 4), _f64(w).ravel()
         n = len(w)
-        r = np.empty(n); J = np.empty((n, 3)) if jac else None
+        if out is not None:
+            r, J = out
+        else:
+            r = np.empty(n); J = np.empty((n, 3)) if jac else None
         s = C.c_double(0.0)
         self.check(lib().pcd_residual_jacobian_batch(self._h, _ptr(p), _ptr(abcd), _ptr(w), C.c_int64(n), _ptr(r), _ptr(J),
                                                      C.byref(s) if want_sum else None), "pcd_residual_jacobian_batch")
@@ -138,9 +157,9 @@ class Context:
                                                           C.c_int64(n), _ptr(r), _ptr(Jp), _ptr(Jq)), "pcd_residual_pose_jacobian_batch")
         return r, Jp, Jq
 
-    def weights_from_type(self, type_, w_proj, w_icp, w_ground):
+    def weights_from_type(self, type_, w_proj, w_icp, w_ground, out=None):
         t = np.ascontiguousarray(type_, dtype=np.uint8)
-        w = np.empty(len(t))
+        w = out if out is not None else np.empty(len(t))
         self.check(lib().pcd_weights_from_type(self._h, _ptr(t), C.c_int64(len(t)), C.c_double(w_proj), C.c_double(w_icp),
                                                C.c_double(w_ground), _ptr(w)), "pcd_weights_from_type")
         return w
@@ -237,13 +256,13 @@ class Cloud:
         return l, ok.astype(bool)
 
     # -- a6 ---------------------------------------------------------------------------------
-    def associate(self, p, range_=None, opt_num=None, sweep=None, variant=ASSOC_LOCAL, fields=None):
+    def associate(self, p, range_=None, opt_num=None, sweep=None, variant=ASSOC_LOCAL, fields=None, out=None):
         p = _f64(p, 3); n = len(p)
         allf = ("idx", "accepted", "type", "rgb", "xyz", "abcd", "dist", "angle")
         fields = allf if fields is None else fields
         shapes = {"idx": ((n,), np.int32), "accepted": ((n,), np.uint8), "type": ((n,), np.uint8), "rgb": ((n, 3), np.uint8),
                   "xyz": ((n, 3), np.float64), "abcd": ((n, 4), np.float64), "dist": ((n,), np.float64), "angle": ((n,), np.float64)}
-        res = {f: np.empty(*shapes[f]) for f in fields}
+        res = out if out is not None else {f: np.empty(*shapes[f]) for f in fields}
         out = AssocOut(*[res[f].ctypes.data if f in res else None for f in allf])
         r = None if range_ is None else _f64(np.broadcast_to(range_, (n,))).ravel()
         on = None if opt_num is None else np.ascontiguousarray(opt_num, dtype=np.int32)
@@ -292,6 +311,21 @@ class Cloud:
         self.ctx.check(lib().pcd_ray_plane_batch(self._h, C.byref(image), _ptr(f), _ptr(w), C.c_int64(n), _ptr(m), _ptr(xyz)),
                        "pcd_ray_plane_batch")
         return m.astype(bool), xyz
+
+
+def pinned_empty(shape, dtype):
+    """numpy array over cudaMallocHost memory (pcd_host_alloc); freed when the array is collected."""
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape)) * dtype.itemsize
+    p = C.c_void_p()
+    rc = lib().pcd_host_alloc(C.byref(p), C.c_int64(max(n, 1)))
+    if rc:
+        raise PcdError(f"pcd_host_alloc failed ({rc}): {lib().pcd_last_error(None).decode()}")
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    a = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    weakref.finalize(buf, lambda q=p.value: lib().pcd_host_free(C.c_void_p(q)))
+    return a
+
 
 
 def splat_coef(cam, opt):

@@ -73,6 +73,20 @@ PCD_API int pcd_ctx_device(const pcd_ctx* ctx);
 /* Counters since creation: [0] queries answered, [1] accepted, [2] ground, [3] kernels launched. */
 PCD_API int pcd_ctx_counters(const pcd_ctx* ctx, int64_t out[4]);
 PCD_API int64_t pcd_ctx_launches(const pcd_ctx* ctx);      /* number of kernels this ctx launched */
+/* Per-kernel device timing for bench.py's roofline: when enabled, every launch of the kernel
+ * classes below is bracketed by CUDA events on its launching stream.  pcd_ctx_kernel_time
+ * synchronises the pending events and returns the accumulated milliseconds and launch count
+ * since the last pcd_ctx_profile(ctx, 1). */
+enum {
+  PCD_K_NN_KEYSORT = 0,   /* query cell keys + radix sort                       */
+  PCD_K_NN_SEARCH = 1,    /* k_nn_search (the dominant kernel)                  */
+  PCD_K_ASSOC_RECORD = 2, /* k_assoc_record                                     */
+  PCD_K_RESJAC = 3,       /* k_resjac (+ partial-sum reduction)                 */
+  PCD_K_PROJECT = 4,      /* k_project (z-buffer splat)                         */
+  PCD_K_COUNT = 8
+};
+PCD_API int pcd_ctx_profile(pcd_ctx* ctx, int enable);
+PCD_API int pcd_ctx_kernel_time(pcd_ctx* ctx, int which, double* total_ms, int64_t* launches);
 /* Pinned host memory for callers that want truly asynchronous staging. */
 PCD_API int pcd_host_alloc(void** out, int64_t bytes);
 PCD_API void pcd_host_free(void* p);
@@ -167,6 +181,8 @@ PCD_API int pcd_residual_pose_jacobian_batch(pcd_ctx* ctx, const double* p_cam, 
 /* Weight by type, src/optim/bundle_adjustment.cc:1013-1028. w_out[n]; type NONE -> 0. */
 PCD_API int pcd_weights_from_type(pcd_ctx* ctx, const uint8_t* type, int64_t n, double w_proj, double w_icp,
                                   double w_ground, double* w_out);
+PCD_API int pcd_weights_from_type_dev(pcd_ctx* ctx, const uint8_t* d_type, int64_t n, double w_proj, double w_icp,
+                                      double w_ground, double* d_w_out, void* stream);
 /* Reconstruction::FilterLidarOutlier distance test (src/base/reconstruction.cc:771-804). */
 PCD_API int pcd_filter_outliers_batch(pcd_ctx* ctx, const double* p_xyz, const double* lidar_xyz, const uint8_t* type,
                                       int64_t n, double max_proj_dist, double max_icp_dist, uint8_t* erase, int64_t* n_erased);

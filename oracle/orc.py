@@ -130,11 +130,14 @@ def match_proj(p, cand):
     return bool(ok), xyz, abcd, d.value, a.value
 
 
-def resjac(p, abcd, w, jac=True):
+def resjac(p, abcd, w, jac=True, threads=1):
     p, abcd, w = _f64(p, 3), _f64(abcd, 4), _f64(w).ravel()
     n = len(w)
     r = np.empty(n); J = np.empty((n, 3)) if jac else None
-    lib().orc_resjac(_p(p), _p(abcd), _p(w), C.c_int64(n), _p(r), _p(J))
+    if threads == 1:
+        lib().orc_resjac(_p(p), _p(abcd), _p(w), C.c_int64(n), _p(r), _p(J))
+    else:
+        lib().orc_resjac_mt(_p(p), _p(abcd), _p(w), C.c_int64(n), _p(r), _p(J), C.c_int(threads))
     return r, J
 
 

@@ -448,6 +448,21 @@ ORC_API void orc_resjac(const double* p, const double* abcd, const double* w, in
   }
 }
 
+/* Same evaluation spread over host threads (what Ceres does with num_threads > 1,
+ * src/optim/bundle_adjustment.cc:515-530); used only by the timed CPU baseline. */
+ORC_API void orc_resjac_mt(const double* p, const double* abcd, const double* w, int64_t n, double* r, double* J, int nthreads) {
+#ifdef _OPENMP
+  if (nthreads <= 0) nthreads = omp_get_max_threads();
+#endif
+  const int64_t blk = 4096;
+  const int64_t nb = (n + blk - 1) / blk;
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+  for (int64_t b = 0; b < nb; b++) {
+    int64_t lo = b * blk, m = (n - lo < blk) ? (n - lo) : blk;
+    orc_resjac(p + 3 * lo, abcd + 4 * lo, w + lo, m, r + lo, J ? J + 3 * lo : 0);
+  }
+}
+
 /* N2 Reconstruction::FilterLidarOutlier distance test     src/base/reconstruction.cc:771-804 */
 ORC_API int64_t orc_filter_outliers(const double* p, const double* lidar_xyz, const uint8_t* type, int64_t n,
                                     double max_proj, double max_icp, uint8_t* erase) {
