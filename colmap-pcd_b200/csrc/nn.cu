@@ -82,12 +82,14 @@ struct Searcher {
 
   __device__ __forceinline__ float group_min_d2() const {
     float d = best_d2();
+    if constexpr (G == 1) return d;
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) d = fminf(d, __shfl_xor_sync(gmask, d, o, 32));
     return d;
   }
 
   __device__ __forceinline__ void group_reduce_best() {
+    if constexpr (G == 1) return;
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) {
       unsigned long long other = __shfl_xor_sync(gmask, best, o, 32);
@@ -111,6 +113,7 @@ struct Searcher {
 
   // scan every entry whose owner lane reported a non-empty range
   __device__ __forceinline__ void run_batch(bool ok, uint32_t b, uint32_t e) {
+    if constexpr (G == 1) { if (ok) scan(b, e); return; }
     unsigned has = (__ballot_sync(gmask, ok) & gmask) >> gbase;
     while (has) {
       int l = __ffs(has) - 1; has &= has - 1;
@@ -159,7 +162,7 @@ struct Searcher {
           if (x >= 0 && x < g.dx) ok = entry_range(x, x, cy + dy, cz + dz, bound2, b, e);
         }
       }
-      unsigned any = __ballot_sync(gmask, ok) & gmask;
+      unsigned any = (G == 1) ? (unsigned)ok : (__ballot_sync(gmask, ok) & gmask);
       if (any) {
         run_batch(ok, b, e);
         bound2 = fminf(group_min_d2(), R2);
@@ -310,7 +313,8 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   if (d_opt_num && !sweep) PCD_FAIL(ctx, PCD_E_INVALID, "opt_num given without a range sweep");
   const GridView& g = cloud->grid;
   const uint32_t* order = nullptr;
-  static int group = [] { const char* e = getenv("PCD_B200_NN_GROUP"); return e ? atoi(e) : 0; }();
+  const char* genv = getenv("PCD_B200_NN_GROUP");   // tuning knob (tools/explore_nn.py)
+  const int group = genv ? atoi(genv) : 0;
   int G = group ? group : g_nn_group;
   if (n > 2048) {
     ProfScope ps(ctx, PCD_K_NN_KEYSORT, st);
@@ -339,6 +343,8 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   const float4* aos = (const float4*)cloud->aos;
   ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
   switch (G) {
+    case 1: launch_nn<1>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
+    case 2: launch_nn<2>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
     case 4: launch_nn<4>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
     case 16: launch_nn<16>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
     case 32: launch_nn<32>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
