@@ -78,7 +78,7 @@ __global__ void k_grid_keys(const float4* __restrict__ aos, int64_t n, pcd::Grid
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   float4 a = aos[2 * i];
-  int cx = cell_of(a.x, g.ox, g.inv_c, g.dx), cy = cell_of(a.y, g.oy, g.inv_c, g.dy), cz = cell_of(a.z, g.oz, g.inv_c, g.dz);
+  int cx = cell_of(a.x, g.ox, g.inv_cx, g.dx), cy = cell_of(a.y, g.oy, g.inv_c, g.dy), cz = cell_of(a.z, g.oz, g.inv_c, g.dz);
   keys[i] = (uint32_t)(((int64_t)cz * g.dy + cy) * g.dx + cx);
   vals[i] = (uint32_t)i;
 }
@@ -98,6 +98,17 @@ __global__ void k_grid_gather(const float4* __restrict__ aos, const uint32_t* __
   float4 a = aos[2 * (int64_t)o];
   pts[i] = make_float4(a.x, a.y, a.z, __uint_as_float(o));
   atomicAdd(&counts[skeys[i]], 1u);
+}
+
+// occupancy words of the 4x4x4-cell blocks (far-query pruning in nn.cu)
+__global__ void k_grid_occupancy(const float4* __restrict__ pts, int64_t n, pcd::GridView g, unsigned long long* __restrict__ occ) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float4 a = pts[i];
+  int cx = cell_of(a.x, g.ox, g.inv_cx, g.dx) / g.xs, cy = cell_of(a.y, g.oy, g.inv_c, g.dy), cz = cell_of(a.z, g.oz, g.inv_c, g.dz);
+  int64_t w = ((int64_t)(cz >> 2) * g.nby + (cy >> 2)) * g.nbx + (cx >> 2);
+  unsigned long long bit = 1ull << ((((cz & 3) << 2) | (cy & 3)) << 2 | (cx & 3));
+  if (!(occ[w] & bit)) atomicOr(&occ[w], bit);
 }
 
 // ---- sub-map (a9): key = round(coord / len), y <-> height, z <-> width (pcd_projection.h:67-73)
@@ -195,7 +206,7 @@ void pcd_cloud_destroy(pcd_cloud* c) {
   if (!c) return;
   DeviceGuard g(c->ctx->device);
   cudaDeviceSynchronize();
-  cudaFree(c->aos); cudaFree(c->grid_pts); cudaFree(c->cell_start);
+  cudaFree(c->aos); cudaFree(c->grid_pts); cudaFree(c->cell_start); cudaFree(c->occ);
   cudaFree(c->sub_keys); cudaFree(c->sub_start); cudaFree(c->sub_pts);
   delete c;
 }
@@ -224,16 +235,20 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
   DeviceGuard g(ctx->device);
   cudaStream_t st = ctx->stream;
   const int64_t n = c->n;
-  if (c->has_index) { cudaFree(c->grid_pts); cudaFree(c->cell_start); c->grid_pts = nullptr; c->cell_start = nullptr; c->has_index = false; }
+  if (c->has_index) { cudaFree(c->grid_pts); cudaFree(c->cell_start); cudaFree(c->occ); c->grid_pts = nullptr; c->cell_start = nullptr; c->occ = nullptr; c->has_index = false; }
   pcd::GridView& G = c->grid;
   memset(&G, 0, sizeof G);
   if (n == 0) {
-    G.c = 1.0f; G.inv_c = 1.0f; G.dx = G.dy = G.dz = 1; G.n = 0; c->n_cells = 1;
+    G.c = 1.0f; G.inv_c = 1.0f; G.cx = 1.0f; G.inv_cx = 1.0f; G.xs = 1; G.dx = G.dy = G.dz = 1; G.n = 0; c->n_cells = 1;
     PCD_CUDA(ctx, cudaMalloc(&c->grid_pts, 16));
     PCD_CUDA(ctx, cudaMalloc(&c->cell_start, 2 * sizeof(uint32_t)));
     PCD_CUDA(ctx, cudaMemsetAsync(c->cell_start, 0, 2 * sizeof(uint32_t), st));
     PCD_CUDA(ctx, cudaStreamSynchronize(st));
-    G.pts = c->grid_pts; G.cell_start = c->cell_start; c->has_index = true;
+    G.nbx = G.nby = G.nbz = 1;
+    PCD_CUDA(ctx, cudaMalloc(&c->occ, 8));
+    PCD_CUDA(ctx, cudaMemsetAsync(c->occ, 0, 8, st));
+    PCD_CUDA(ctx, cudaStreamSynchronize(st));
+    G.pts = c->grid_pts; G.cell_start = c->cell_start; G.occ = c->occ; c->has_index = true;
     return PCD_OK;
   }
   // bbox
@@ -261,18 +276,22 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
   PCD_CUDA(ctx, ctx->vals.ensure(sizeof(uint32_t) * (size_t)n));
   PCD_CUDA(ctx, ctx->vals_alt.ensure(sizeof(uint32_t) * (size_t)n));
 
+  int xsub = 4;                                  // x cells per (y, z) cell edge; power of two
+  if (const char* e = getenv("PCD_B200_XSUB")) { int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) xsub = v; }
   auto setup = [&](float cs) -> bool {   // fills G dims for cell edge cs; false if too many cells
     G.c = cs; G.inv_c = 1.0f / cs;
+    G.xs = xsub; G.cx = cs / (float)xsub; G.inv_cx = G.inv_c * (float)xsub;
     G.ox = c->bb_lo[0]; G.oy = c->bb_lo[1]; G.oz = c->bb_lo[2];
     double dims[3];
-    for (int d = 0; d < 3; d++) dims[d] = floor((double)(c->bb_hi[d] - c->bb_lo[d]) * G.inv_c) + 1.0;
+    for (int d = 0; d < 3; d++) dims[d] = floor((double)(c->bb_hi[d] - c->bb_lo[d]) * (d == 0 ? G.inv_cx : G.inv_c)) + 1.0;
     double total = dims[0] * dims[1] * dims[2];
     if (total > 2.0e9 || dims[0] > 2.0e6 || dims[1] > 2.0e6 || dims[2] > 2.0e6) return false;
     G.dx = (int)dims[0]; G.dy = (int)dims[1]; G.dz = (int)dims[2];
     c->n_cells = (int64_t)G.dx * G.dy * G.dz;
     // float cell assignment error: one rounding of (p - o), magnitude <= 2^-24 * |p - o|.
-    G.margin_cells = 1e-3f + 8.0f * (ext + absmax) * 1.2e-7f * G.inv_c;
+    G.margin = 1e-3f * G.cx + 8.0f * (ext + absmax) * 1.2e-7f;
     G.n = (uint32_t)n;
+    G.nbx = ((G.dx + xsub - 1) / xsub + 3) / 4; G.nby = (G.dy + 3) / 4; G.nbz = (G.dz + 3) / 4;
     return true;
   };
 
@@ -314,7 +333,7 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
       unsigned long long uniq = 1;
       PCD_CUDA(ctx, cudaMemcpyAsync(&uniq, d_cnt, 8, cudaMemcpyDeviceToHost, st));
       PCD_CUDA(ctx, cudaStreamSynchronize(st));
-      double occ = (double)n / (double)(uniq ? uniq : 1);
+      double occ = (double)n / (double)(uniq ? uniq : 1) * (double)xsub;   // per (y, z)-sized cell
       int dir = occ < lo_occ ? +1 : (occ >= hi_occ ? -1 : 0);
       if (dir == 0) break;
       if (last_dir != 0 && dir != last_dir) {          // overshoot: settle on the coarser cell
@@ -342,8 +361,15 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
     PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
     PCD_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, c->cell_start, c->cell_start, (int)(c->n_cells + 1), st));
   }
+  {
+    size_t words = (size_t)G.nbx * G.nby * G.nbz;
+    PCD_CUDA(ctx, cudaMalloc(&c->occ, 8 * words));
+    PCD_CUDA(ctx, cudaMemsetAsync(c->occ, 0, 8 * words, st));
+    k_grid_occupancy<<<pcd_blocks(n, 256), 256, 0, st>>>(c->grid_pts, n, G, c->occ);
+    PCD_LAUNCH_CHECK(ctx);
+  }
   PCD_CUDA(ctx, cudaStreamSynchronize(st));
-  G.pts = c->grid_pts; G.cell_start = c->cell_start;
+  G.pts = c->grid_pts; G.cell_start = c->cell_start; G.occ = c->occ;
   c->has_index = true;
   return PCD_OK;
 }

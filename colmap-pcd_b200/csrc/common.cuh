@@ -48,9 +48,15 @@ struct GridView {
   const float4* pts;            // cell-sorted: x, y, z, __int_as_float(original index)
   const uint32_t* cell_start;   // n_cells + 1 offsets into pts
   float ox, oy, oz;             // origin = bbox min
-  float c, inv_c;               // cell edge (power of two) and its reciprocal
-  int dx, dy, dz;               // grid dimensions (x fastest)
-  float margin_cells;           // conservative slack (in cells) for float cell assignment
+  float c, inv_c;               // cell edge along y and z (power of two) and its reciprocal
+  float cx, inv_cx;             // cell edge along x = c / xs: rows are contiguous along x, so a finer
+  int xs;                       //   x resolution narrows the candidate run at no extra lookup cost
+  int dx, dy, dz;               // grid dimensions (x fastest; dx counts x cells of edge cx)
+  float margin;                 // conservative slack (metres) for the float cell assignment
+  // occupancy pyramid for far queries: one 64-bit word per block of 4 x 4 x 4 cubic cells of edge c
+  // (x cell = ix / xs); bit (lz * 4 + ly) * 4 + lx is set iff the cell holds a point
+  const unsigned long long* occ;
+  int nbx, nby, nbz;
   uint32_t n;
 };
 
@@ -78,7 +84,7 @@ struct pcd_ctx {
   pcd::DevBuf keys, keys_alt, vals, vals_alt, cub_tmp, misc, partial;
   pcd::DevBuf stage_in[2], stage_out[2], stage_aux[2];
   pcd::PinBuf pin_in[2], pin_out[2];
-  pcd::DevBuf img_buf, feat_buf, zbuf, sel_buf;
+  pcd::DevBuf img_buf, feat_buf, zbuf, sel_buf, far_q;
   // optional per-kernel CUDA-event timing (pcd_ctx_profile); spans are resolved lazily
   bool prof = false;
   struct Span { cudaEvent_t a, b; int which; };
@@ -117,6 +123,7 @@ struct pcd_cloud {
   bool has_index = false;
   float4* grid_pts = nullptr;
   uint32_t* cell_start = nullptr;
+  unsigned long long* occ = nullptr;
   pcd::GridView grid = {};
   int64_t n_cells = 0;
   float bb_lo[3] = {0, 0, 0}, bb_hi[3] = {0, 0, 0};

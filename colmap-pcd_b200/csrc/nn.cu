@@ -3,19 +3,28 @@
 // float-cast query, src/lidar/ply.cc:92; ties -> lowest original index).
 //
 // Pipeline per batch:  k_query_keys -> cub radix sort (cell id, query id) -> k_nn_search.
-// k_nn_search: G lanes cooperate on one query.  A CTA owns a contiguous chunk of the
-// cell-sorted queries (neighbouring queries share cells -> L1/L2 reuse).
-//   phase 1: the 3x3x3 block around the query cell as 9 x-runs (x is the fastest grid axis, so
-//            cells x-1..x+1 of one (y,z) row are ONE contiguous range of the sorted points:
-//            2 cell_start loads per row, coalesced float4 point loads).
-//   phase 2: queries that the block could not certify (best distance > distance to the block
-//            faces) are compacted in shared memory and continue shell by shell (k = 2, 3, ...)
-//            until certified, bounded by their search radius, or the grid is exhausted.
-// Exactness: a row/shell is skipped only when a conservative lower bound on its distance
-// (cell geometry minus a float-rounding margin) exceeds the current best.
+// The grid is anisotropic: cells are c x c in (y, z) and c / xs along x.  A (y, z) row of cells
+// is ONE contiguous range of the cell-sorted points, so any x interval of a row costs two
+// cell_start loads, and the finer x resolution only narrows the interval that is scanned.
+//
+// k_nn_search, one CTA per contiguous chunk of the cell-sorted queries (neighbouring queries
+// share cells, so their candidate loads hit the same L1 lines / sectors):
+//   phase 1: ONE THREAD PER QUERY.  Own cell first (gives a distance bound), then the rows of the
+//            (2*K1+1)^2 (y, z) neighbourhood in order of increasing distance; a row is skipped when
+//            its distance lower bound exceeds the current best, and its x interval is clipped to
+//            the chord of the current best-distance ball.
+//   phase 2: the few queries the K1 block could not certify (best distance > distance to the
+//            block faces: outliers far from every surface) are compacted in shared memory and
+//            handled one WARP per query, best-first over the occupancy words of 4x4x4-cell blocks:
+//            empty space costs one 8-byte load per 64 cells, and only cells whose box distance
+//            beats the current best are ever scanned.
+// Exactness: a row / interval is skipped only when a conservative lower bound on its distance
+// (cell geometry minus a float-rounding margin) exceeds the current best, so every point that
+// could win or tie is examined; the winner is min over (d2 bits << 32 | original index).
 #include "nn.cuh"
 #include <cub/cub.cuh>
 #include <math.h>
+#include <stdlib.h>
 
 namespace pcd {
 
@@ -39,7 +48,7 @@ __global__ void k_query_keys(const double* __restrict__ q, int64_t n, GridView g
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   float x = (float)q[3 * i], y = (float)q[3 * i + 1], z = (float)q[3 * i + 2];
-  int cx = clampi((int)floorf((x - g.ox) * g.inv_c), 0, g.dx - 1);
+  int cx = clampi((int)floorf((x - g.ox) * g.inv_cx), 0, g.dx - 1);
   int cy = clampi((int)floorf((y - g.oy) * g.inv_c), 0, g.dy - 1);
   int cz = clampi((int)floorf((z - g.oz) * g.inv_c), 0, g.dz - 1);
   keys[i] = (uint32_t)(((int64_t)cz * g.dy + cy) * g.dx + cx);
@@ -47,24 +56,23 @@ __global__ void k_query_keys(const double* __restrict__ q, int64_t n, GridView g
 }
 
 constexpr int NN_THREADS = 256;
-constexpr int NN_MAX_CHUNK = 1024;
+constexpr float SHRINK = 0.999999f;   // applied to lower bounds before comparing with a float d2
+constexpr float GROW = 1.000001f;
 
-template <int G>
-struct Searcher {
-  const GridView& g;
-  float qx, qy, qz, tx, ty, tz;
-  int cx, cy, cz;
-  float R2;                 // conservative float bound on radius^2 (INFINITY when unbounded)
-  unsigned long long best;  // (float bits of d2 << 32) | original index
-  unsigned gmask; int gl, gbase;
-
-  __device__ __forceinline__ Searcher(const GridView& g_) : g(g_) {}
+// Per-query search state.  All geometry is in metres relative to the grid origin.
+struct Query {
+  float qx, qy, qz;          // float-cast query (the reference's cast, ply.cc:92)
+  float px, py, pz;          // q - origin
+  int ix, iy, iz;            // own cell (clamped into the grid)
+  float R2;                  // conservative float bound on radius^2 (INFINITY when unbounded)
+  unsigned long long best;   // (float bits of d2 << 32) | original index
 
   __device__ __forceinline__ float best_d2() const { return __uint_as_float((unsigned)(best >> 32)); }
+  __device__ __forceinline__ float bound2() const { return fminf(best_d2(), R2); }
 
-  __device__ __forceinline__ void scan(uint32_t b, uint32_t e) {
+  __device__ __forceinline__ void scan(const GridView& g, uint32_t b, uint32_t e, int first, int stride) {
     unsigned long long bst = best;
-    for (uint32_t j = b + gl; j < e; j += G) {
+    for (uint32_t j = b + first; j < e; j += stride) {
       float4 p = __ldg(&g.pts[j]);
       float ddx = qx - p.x, ddy = qy - p.y, ddz = qz - p.z;
       float d = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
@@ -74,128 +82,46 @@ struct Searcher {
     best = bst;
   }
 
-  // lower bound (in cells) on the distance along one axis from the query to cells [lo, hi]
-  __device__ __forceinline__ float gap(float t, int lo, int hi) const {
-    float a = fmaxf((float)lo - t, t - (float)(hi + 1));
-    return fmaxf(a - g.margin_cells, 0.0f);
+  // lower bound (metres) on the distance along one axis from coordinate p to cells [lo, hi] of edge c
+  static __device__ __forceinline__ float gap(float p, int lo, int hi, float c, float margin) {
+    float a = fmaxf((float)lo * c - p, p - (float)(hi + 1) * c);
+    return fmaxf(a - margin, 0.0f);
   }
 
-  __device__ __forceinline__ float group_min_d2() const {
-    float d = best_d2();
-    if constexpr (G == 1) return d;
-#pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) d = fminf(d, __shfl_xor_sync(gmask, d, o, 32));
-    return d;
+  // x interval [x0, x1] (cells of edge cx) clipped to the chord of the ball of squared radius b2 at
+  // squared (y, z) offset g2, and to the grid
+  __device__ __forceinline__ bool chord(const GridView& g, float b2, float g2, int& x0, int& x1) const {
+    float hx = sqrtf(b2 - g2) * GROW + g.margin;          // INFINITY stays INFINITY
+    x0 = max(max(x0, 0), (int)floorf((px - hx) * g.inv_cx));
+    x1 = min(min(x1, g.dx - 1), (int)floorf((px + hx) * g.inv_cx));
+    return x0 <= x1;
   }
 
-  __device__ __forceinline__ void group_reduce_best() {
-    if constexpr (G == 1) return;
-#pragma unroll
-    for (int o = G / 2; o > 0; o >>= 1) {
-      unsigned long long other = __shfl_xor_sync(gmask, best, o, 32);
-      best = other < best ? other : best;
-    }
-  }
-
-  // range of one entry: cells x0..x1 of row (y, z); returns false when empty/out of grid/pruned
-  __device__ __forceinline__ bool entry_range(int x0, int x1, int y, int z, float bound2, uint32_t& b, uint32_t& e) const {
-    if (y < 0 || y >= g.dy || z < 0 || z >= g.dz) return false;
-    x0 = max(x0, 0); x1 = min(x1, g.dx - 1);
-    if (x0 > x1) return false;
-    float gx = gap(tx, x0, x1), gy = gap(ty, y, y), gz = gap(tz, z, z);
-    float rm = (gx * gx + gy * gy + gz * gz) * (g.c * g.c) * 0.999999f;
-    if (rm > bound2) return false;
-    uint32_t lin = ((uint32_t)z * (uint32_t)g.dy + (uint32_t)y) * (uint32_t)g.dx;
-    b = __ldg(&g.cell_start[lin + x0]);
-    e = __ldg(&g.cell_start[lin + x1 + 1]);
-    return b < e;
-  }
-
-  // scan every entry whose owner lane reported a non-empty range
-  __device__ __forceinline__ void run_batch(bool ok, uint32_t b, uint32_t e) {
-    if constexpr (G == 1) { if (ok) scan(b, e); return; }
-    unsigned has = (__ballot_sync(gmask, ok) & gmask) >> gbase;
-    while (has) {
-      int l = __ffs(has) - 1; has &= has - 1;
-      uint32_t bb = __shfl_sync(gmask, b, gbase + l, 32);
-      uint32_t ee = __shfl_sync(gmask, e, gbase + l, 32);
-      scan(bb, ee);
-    }
-  }
-
-  // phase 1: the 3x3x3 block as nine full x-runs, centre row first
-  __device__ __forceinline__ void scan_block1() {
-    uint32_t b = 0, e = 0;
-    // centre row: every lane loads the same two offsets (broadcast)
-    if (entry_range(cx - 1, cx + 1, cy, cz, R2, b, e)) scan(b, e);
-    float bound2 = fminf(group_min_d2(), R2);
-#pragma unroll
-    for (int base = 0; base < 8; base += G) {
-      int r = base + gl;            // 0..7 -> the eight non-centre rows
-      bool ok = false;
-      if (r < 8) {
-        int rr = r + (r >= 4);      // skip index 4 (dy = dz = 0)
-        int dy = rr % 3 - 1, dz = rr / 3 - 1;
-        ok = entry_range(cx - 1, cx + 1, cy + dy, cz + dz, bound2, b, e);
-      }
-      run_batch(ok, b, e);
-      if (base + G < 8) bound2 = fminf(group_min_d2(), R2);
-    }
-    group_reduce_best();
-  }
-
-  // shell k >= 2: boundary rows as full runs, interior rows as their two end cells
-  __device__ __forceinline__ void scan_shell(int k) {
-    const int W = 2 * k + 1, nent = 2 * W * W;
-    float bound2 = fminf(group_min_d2(), R2);
-    for (int base = 0; base < nent; base += G) {
-      int ent = base + gl;
-      bool ok = false; uint32_t b = 0, e = 0;
-      if (ent < nent) {
-        int row = ent >> 1, seg = ent & 1;
-        int dy = row % W - k, dz = row / W - k;
-        bool boundary = (abs(dy) == k) || (abs(dz) == k);
-        if (boundary) {
-          if (seg == 0) ok = entry_range(cx - k, cx + k, cy + dy, cz + dz, bound2, b, e);
-        } else {
-          int x = seg == 0 ? cx - k : cx + k;
-          if (x >= 0 && x < g.dx) ok = entry_range(x, x, cy + dy, cz + dz, bound2, b, e);
-        }
-      }
-      unsigned any = (G == 1) ? (unsigned)ok : (__ballot_sync(gmask, ok) & gmask);
-      if (any) {
-        run_batch(ok, b, e);
-        bound2 = fminf(group_min_d2(), R2);
-      }
-    }
-    group_reduce_best();
-  }
-
-  // squared radius (metres^2) within which the (2k+1)^3 block is known to hold every point
-  __device__ __forceinline__ float certified2(int k) const {
+  // squared radius (metres^2) within which the block x: +-kx cells, y/z: +-k cells around the own
+  // cell is known to hold every cloud point; INFINITY when the block covers the grid
+  __device__ __forceinline__ float certified2(const GridView& g, int kx, int k) const {
     float rc = INFINITY;
-    if (cx - k > 0) rc = fminf(rc, tx - (float)(cx - k));
-    if (cx + k < g.dx - 1) rc = fminf(rc, (float)(cx + k + 1) - tx);
-    if (cy - k > 0) rc = fminf(rc, ty - (float)(cy - k));
-    if (cy + k < g.dy - 1) rc = fminf(rc, (float)(cy + k + 1) - ty);
-    if (cz - k > 0) rc = fminf(rc, tz - (float)(cz - k));
-    if (cz + k < g.dz - 1) rc = fminf(rc, (float)(cz + k + 1) - tz);
+    if (ix - kx > 0) rc = fminf(rc, px - (float)(ix - kx) * g.cx);
+    if (ix + kx < g.dx - 1) rc = fminf(rc, (float)(ix + kx + 1) * g.cx - px);
+    if (iy - k > 0) rc = fminf(rc, py - (float)(iy - k) * g.c);
+    if (iy + k < g.dy - 1) rc = fminf(rc, (float)(iy + k + 1) * g.c - py);
+    if (iz - k > 0) rc = fminf(rc, pz - (float)(iz - k) * g.c);
+    if (iz + k < g.dz - 1) rc = fminf(rc, (float)(iz + k + 1) * g.c - pz);
     if (rc == INFINITY) return INFINITY;
-    rc = fmaxf(rc - g.margin_cells, 0.0f) * g.c;
-    return rc * rc * 0.999999f;
+    rc = fmaxf(rc - g.margin, 0.0f);
+    return rc * rc * SHRINK;
   }
-
 
   // loads query `i`, derives its cell, radius bound and validity
-  __device__ __forceinline__ bool load_query(const double* __restrict__ q, const RadiusSrc& rs, uint32_t i,
-                                             double& px, double& py, double& pz, double& R) {
-    px = q[3 * (int64_t)i]; py = q[3 * (int64_t)i + 1]; pz = q[3 * (int64_t)i + 2];
+  __device__ __forceinline__ bool load(const GridView& g, const double* __restrict__ q, const RadiusSrc& rs, uint32_t i,
+                                       double& dx, double& dy, double& dz, double& R) {
+    dx = q[3 * (int64_t)i]; dy = q[3 * (int64_t)i + 1]; dz = q[3 * (int64_t)i + 2];
     R = query_radius(rs, i);
-    qx = (float)px; qy = (float)py; qz = (float)pz;
-    tx = (qx - g.ox) * g.inv_c; ty = (qy - g.oy) * g.inv_c; tz = (qz - g.oz) * g.inv_c;
-    cx = clampi((int)floorf(tx), 0, g.dx - 1);
-    cy = clampi((int)floorf(ty), 0, g.dy - 1);
-    cz = clampi((int)floorf(tz), 0, g.dz - 1);
+    qx = (float)dx; qy = (float)dy; qz = (float)dz;
+    px = qx - g.ox; py = qy - g.oy; pz = qz - g.oz;
+    ix = clampi((int)floorf(px * g.inv_cx), 0, g.dx - 1);
+    iy = clampi((int)floorf(py * g.inv_c), 0, g.dy - 1);
+    iz = clampi((int)floorf(pz * g.inv_c), 0, g.dz - 1);
     if (R == INFINITY) R2 = INFINITY;
     else {
       float Rf = __double2float_ru(fmax(R, 0.0));
@@ -204,15 +130,164 @@ struct Searcher {
     bool valid = isfinite(qx) && isfinite(qy) && isfinite(qz) && !(R < 0.0) && !isnan(R) && g.n > 0;
     if (valid && R2 != INFINITY) {
       // no cloud point can be within R of a query farther than R from the grid box
-      float bx = gap(tx, 0, g.dx - 1), by = gap(ty, 0, g.dy - 1), bz = gap(tz, 0, g.dz - 1);
-      if ((bx * bx + by * by + bz * bz) * (g.c * g.c) * 0.999999f > R2) valid = false;
+      float bx = gap(px, 0, g.dx - 1, g.cx, g.margin), by = gap(py, 0, g.dy - 1, g.c, g.margin),
+            bz = gap(pz, 0, g.dz - 1, g.c, g.margin);
+      if ((bx * bx + by * by + bz * bz) * SHRINK > R2) valid = false;
     }
+    best = ~0ull;
     return valid;
   }
 
-  __device__ __forceinline__ bool done(int k) const {
-    float rc2 = certified2(k);
-    return best_d2() <= rc2 || R2 <= rc2;
+  // One row (iy + DY, iz + DZ) of phase 1.  gy2 / gz2: squared axis gaps, NaN for rows outside the grid.
+  __device__ __forceinline__ void row(const GridView& g, int kx, int dy, int dz, float gy2, float gz2) {
+    const float g2 = (gy2 + gz2) * SHRINK;
+    const float b2 = bound2();
+    if (!(g2 <= b2)) return;                               // pruned, or outside the grid (NaN)
+    int x0 = ix - kx, x1 = ix + kx;
+    if (!chord(g, b2, g2, x0, x1)) return;
+    const uint32_t lin = ((uint32_t)(iz + dz) * (uint32_t)g.dy + (uint32_t)(iy + dy)) * (uint32_t)g.dx;
+    const uint32_t b = __ldg(&g.cell_start[lin + x0]);
+    const uint32_t e = __ldg(&g.cell_start[lin + x1 + 1]);
+    scan(g, b, e, 0, 1);
+  }
+
+  // phase 1: own cell, rest of the centre row, then rings 1..K1 of rows; returns true when certified
+  template <int K1>
+  __device__ __forceinline__ bool search_block(const GridView& g) {
+    const int kx = K1 * g.xs;
+    // squared axis gaps to the rows / slabs at offset -K1..K1 (NaN outside the grid -> never scanned)
+    float gy2[2 * K1 + 1], gz2[2 * K1 + 1];
+#pragma unroll
+    for (int d = -K1; d <= K1; d++) {
+      float a = gap(py, iy + d, iy + d, g.c, g.margin), b = gap(pz, iz + d, iz + d, g.c, g.margin);
+      gy2[d + K1] = (iy + d < 0 || iy + d >= g.dy) ? __int_as_float(0x7fc00000) : a * a;
+      gz2[d + K1] = (iz + d < 0 || iz + d >= g.dz) ? __int_as_float(0x7fc00000) : b * b;
+    }
+    // own cell, then the rest of the centre row inside the chord of the bound it gave
+    const uint32_t lin0 = ((uint32_t)iz * (uint32_t)g.dy + (uint32_t)iy) * (uint32_t)g.dx;
+    const uint32_t b0 = __ldg(&g.cell_start[lin0 + ix]), e0 = __ldg(&g.cell_start[lin0 + ix + 1]);
+    scan(g, b0, e0, 0, 1);
+    {
+      int x0 = ix - kx, x1 = ix + kx;
+      chord(g, bound2(), 0.0f, x0, x1);                    // always contains the own cell
+      x0 = min(x0, ix); x1 = max(x1, ix);
+      const uint32_t b = __ldg(&g.cell_start[lin0 + x0]), e = __ldg(&g.cell_start[lin0 + x1 + 1]);
+      scan(g, b, b0, 0, 1);
+      scan(g, e0, e, 0, 1);
+    }
+#pragma unroll
+    for (int k = 1; k <= K1; k++) {
+      // ring k of rows, nearest first: the four axis rows, then the rest of the ring
+#pragma unroll
+      for (int t = 0; t <= k; t++) {
+        // offsets (+-k, +-t) and (+-t, +-k); t = 0 gives the axis rows, t = k the corners
+#pragma unroll
+        for (int s = 0; s < 8; s++) {
+          const int a = (s & 1) ? k : -k, bsgn = (s & 2) ? t : -t;
+          const int dy = (s & 4) ? a : bsgn, dz = (s & 4) ? bsgn : a;
+          if (t == 0 && (s & 2)) continue;                 // +-0 duplicates
+          if (t == k && (s & 4)) continue;                 // corners appear in both orientations
+          row(g, kx, dy, dz, gy2[dy + K1], gz2[dz + K1]);
+        }
+      }
+      const float rc2 = certified2(g, kx, k);
+      if (best_d2() <= rc2 || R2 <= rc2) return true;
+    }
+    return false;
+  }
+};
+
+// ---- phase 2: far queries, one thread per query, best-first over the block occupancy words -----
+struct FarSearch {
+  const GridView& g;
+  Query& Q;
+  float b2;                  // min(R2, best distance so far)
+
+  __device__ __forceinline__ FarSearch(const GridView& g_, Query& Q_) : g(g_), Q(Q_) { b2 = Q.bound2(); }
+
+  // squared lower bound to cubic cell `bit` of block (X, Y, Z)
+  __device__ __forceinline__ float cell_lb2(int X, int Y, int Z, int bit) const {
+    const int cxc = 4 * X + (bit & 3), cy = 4 * Y + ((bit >> 2) & 3), cz = 4 * Z + (bit >> 4);
+    float a = Query::gap(Q.px, cxc * g.xs, cxc * g.xs + g.xs - 1, g.cx, g.margin),
+          b = Query::gap(Q.py, cy, cy, g.c, g.margin), c = Query::gap(Q.pz, cz, cz, g.c, g.margin);
+    return (a * a + (b * b + c * c)) * SHRINK;
+  }
+
+  __device__ __forceinline__ void scan_cell(int X, int Y, int Z, int bit) {
+    const int cxc = 4 * X + (bit & 3), cy = 4 * Y + ((bit >> 2) & 3), cz = 4 * Z + (bit >> 4);
+    float gy = Query::gap(Q.py, cy, cy, g.c, g.margin), gz = Query::gap(Q.pz, cz, cz, g.c, g.margin);
+    float g2 = (gy * gy + gz * gz) * SHRINK;
+    if (!(g2 <= b2)) return;
+    int x0 = cxc * g.xs, x1 = x0 + g.xs - 1;
+    if (!Q.chord(g, b2, g2, x0, x1)) return;
+    const uint32_t lin = ((uint32_t)cz * (uint32_t)g.dy + (uint32_t)cy) * (uint32_t)g.dx;
+    const uint32_t b = __ldg(&g.cell_start[lin + x0]), e = __ldg(&g.cell_start[lin + x1 + 1]);
+    Q.scan(g, b, e, 0, 1);
+    b2 = Q.bound2();
+  }
+
+  // the occupied cells of one block: the nearest first (it usually brings the bound down to the true
+  // distance), then every other cell whose box distance still beats the bound
+  __device__ __forceinline__ void scan_block(int X, int Y, int Z, unsigned long long w) {
+    float best_lb = INFINITY; int best_bit = -1;
+    for (unsigned long long ww = w; ww; ww &= ww - 1) {
+      const int bit = __ffsll((long long)ww) - 1;
+      const float lb = cell_lb2(X, Y, Z, bit);
+      if (lb < best_lb || best_bit < 0) { best_lb = lb; best_bit = bit; }
+    }
+    if (best_bit < 0 || !(best_lb <= b2)) return;
+    scan_cell(X, Y, Z, best_bit);
+    for (unsigned long long ww = w & ~(1ull << best_bit); ww; ww &= ww - 1) {
+      const int bit = __ffsll((long long)ww) - 1;
+      if (cell_lb2(X, Y, Z, bit) <= b2) scan_cell(X, Y, Z, bit);
+    }
+  }
+
+  __device__ __forceinline__ void block(int X, int Y, int Z, float gyz2) {
+    const int sx = 4 * g.xs;
+    float gx = Query::gap(Q.px, X * sx, X * sx + sx - 1, g.cx, g.margin);
+    if (!((gx * gx + gyz2) * SHRINK <= b2)) return;
+    const unsigned long long w = __ldg(&g.occ[((int64_t)Z * g.nby + Y) * g.nbx + X]);
+    if (w) scan_block(X, Y, Z, w);
+  }
+
+  __device__ __forceinline__ void run() {
+    const int bx = (Q.ix / g.xs) >> 2, by = Q.iy >> 2, bz = Q.iz >> 2;
+    const int sx = 4 * g.xs;
+    const int kmax = max(g.nbx, max(g.nby, g.nbz));
+    for (int kb = 0; kb <= kmax; kb++) {
+      // the shell of blocks at Chebyshev distance kb, clamped to the grid
+      const int Z0 = max(bz - kb, 0), Z1 = min(bz + kb, g.nbz - 1), Y0 = max(by - kb, 0), Y1 = min(by + kb, g.nby - 1);
+      const int X0 = max(bx - kb, 0), X1 = min(bx + kb, g.nbx - 1);
+      for (int Z = Z0; Z <= Z1; Z++) {
+        const float gz = Query::gap(Q.pz, 4 * Z, 4 * Z + 3, g.c, g.margin);
+        if (!(gz * gz * SHRINK <= b2)) continue;
+        for (int Y = Y0; Y <= Y1; Y++) {
+          const float gy = Query::gap(Q.py, 4 * Y, 4 * Y + 3, g.c, g.margin);
+          const float gyz2 = gy * gy + gz * gz;
+          if (!(gyz2 * SHRINK <= b2)) continue;
+          if (abs(Z - bz) == kb || abs(Y - by) == kb) {
+            for (int X = X0; X <= X1; X++) block(X, Y, Z, gyz2);
+          } else {
+            if (bx - kb >= 0) block(bx - kb, Y, Z, gyz2);
+            if (bx + kb < g.nbx) block(bx + kb, Y, Z, gyz2);
+          }
+        }
+      }
+      // every point outside the cube of shell kb is at least this far (faces on the grid boundary do not count)
+      float rc = INFINITY;
+      const int x0 = (bx - kb) * sx, x1 = (bx + kb + 1) * sx - 1, y0 = 4 * (by - kb), y1 = 4 * (by + kb) + 3,
+                z0 = 4 * (bz - kb), z1 = 4 * (bz + kb) + 3;
+      if (x0 > 0) rc = fminf(rc, Q.px - (float)x0 * g.cx);
+      if (x1 < g.dx - 1) rc = fminf(rc, (float)(x1 + 1) * g.cx - Q.px);
+      if (y0 > 0) rc = fminf(rc, Q.py - (float)y0 * g.c);
+      if (y1 < g.dy - 1) rc = fminf(rc, (float)(y1 + 1) * g.c - Q.py);
+      if (z0 > 0) rc = fminf(rc, Q.pz - (float)z0 * g.c);
+      if (z1 < g.dz - 1) rc = fminf(rc, (float)(z1 + 1) * g.c - Q.pz);
+      if (rc == INFINITY) break;
+      rc = fmaxf(rc - g.margin, 0.0f);
+      if (b2 <= rc * rc * SHRINK) break;
+    }
   }
 };
 
@@ -228,7 +303,7 @@ __device__ __forceinline__ void nn_write(unsigned long long best, double px, dou
     if (R != INFINITY) {
       float4 l = __ldg(&aos[2 * (int64_t)idx]);
       double x = (double)l.x - px, y = (double)l.y - py, z = (double)l.z - pz;
-      double dist = sqrt(x * x + (y * y + z * z));
+      double dist = sqrt(__dadd_rn(__dmul_rn(x, x), __dadd_rn(__dmul_rn(y, y), __dmul_rn(z, z))));
       if (dist > R) { idx = -1; d2 = INFINITY; }
     }
   }
@@ -236,71 +311,54 @@ __device__ __forceinline__ void nn_write(unsigned long long best, double px, dou
   if (d2_out) d2_out[i] = d2;
 }
 
-template <int G>
+// phase 1: one thread per (cell-sorted) query; uncertified queries go to the far queue
+struct FarItem { unsigned long long best; uint32_t i; uint32_t pad; };
+
+template <int K1>
 __global__ void __launch_bounds__(NN_THREADS) k_nn_search(GridView g, const double* __restrict__ q, RadiusSrc rs,
-                                                          const uint32_t* __restrict__ order, int64_t n, int chunk,
+                                                          const uint32_t* __restrict__ order, int64_t n,
                                                           const float4* __restrict__ aos, int32_t* __restrict__ idx_out,
-                                                          float* __restrict__ d2_out) {
-  constexpr int GPC = NN_THREADS / G;   // groups (queries in flight) per CTA
-  __shared__ uint32_t s_slot[NN_MAX_CHUNK];
-  __shared__ unsigned long long s_best[NN_MAX_CHUNK];
-  __shared__ int s_count;
-  if (threadIdx.x == 0) s_count = 0;
-  __syncthreads();
-
-  const int lane = threadIdx.x & 31;
-  Searcher<G> S(g);
-  S.gl = lane & (G - 1);
-  S.gbase = lane & ~(G - 1);
-  S.gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << S.gbase);
-  const int group = threadIdx.x / G;
-  const int64_t cta_lo = (int64_t)blockIdx.x * chunk;
-  const int64_t cta_hi = min(cta_lo + (int64_t)chunk, n);
-
-  // ---------------- phase 1 ----------------
-  for (int64_t slot = cta_lo + group; slot < cta_hi; slot += GPC) {
-    double px, py, pz, R;
-    const uint32_t i = order ? order[slot] : (uint32_t)slot;
-    bool valid = S.load_query(q, rs, i, px, py, pz, R);
-    S.best = ~0ull;
-    bool resolved = true;
-    if (valid) {
-      S.scan_block1();
-      resolved = S.done(1);
+                                                          float* __restrict__ d2_out, FarItem* __restrict__ far,
+                                                          unsigned int* __restrict__ far_count) {
+  const int64_t slot = (int64_t)blockIdx.x * NN_THREADS + threadIdx.x;
+  if (slot >= n) return;
+  double px, py, pz, R;
+  const uint32_t i = order ? order[slot] : (uint32_t)slot;
+  Query Q;
+  const bool valid = Q.load(g, q, rs, i, px, py, pz, R);
+  const bool resolved = valid ? Q.search_block<K1>(g) : true;
+  if (resolved) nn_write(Q.best, px, py, pz, R, aos, i, idx_out, d2_out);
+  // warp-aggregated push of the uncertified queries
+  const unsigned act = __activemask();
+  const unsigned m = __ballot_sync(act, !resolved);
+  if (m) {
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(far_count, (unsigned)__popc(m));
+    base = __shfl_sync(act, base, leader);
+    if (!resolved) {
+      FarItem it; it.best = Q.best; it.i = i; it.pad = 0;
+      far[base + __popc(m & ((1u << lane) - 1u))] = it;
     }
-    if (S.gl == 0) {
-      if (resolved) nn_write(S.best, px, py, pz, R, aos, i, idx_out, d2_out);
-      else {
-        int pos = atomicAdd(&s_count, 1);
-        s_slot[pos] = (uint32_t)(slot - cta_lo);
-        s_best[pos] = S.best;
-      }
-    }
-  }
-  __syncthreads();
-  // ---------------- phase 2 ----------------
-  const int pending = s_count;
-  const int kmax = max(g.dx, max(g.dy, g.dz));
-  for (int e = group; e < pending; e += GPC) {
-    double px, py, pz, R;
-    const int64_t slot = cta_lo + s_slot[e];
-    const uint32_t i = order ? order[slot] : (uint32_t)slot;
-    S.load_query(q, rs, i, px, py, pz, R);
-    S.best = s_best[e];
-    for (int k = 2; k <= kmax; k++) {
-      S.scan_shell(k);
-      if (S.done(k)) break;
-    }
-    if (S.gl == 0) nn_write(S.best, px, py, pz, R, aos, i, idx_out, d2_out);
   }
 }
 
-static int g_nn_group = 8;
-
-template <int G>
-static void launch_nn(int blocks, cudaStream_t st, const GridView& g, const double* q, const RadiusSrc& rs,
-                      const uint32_t* order, int64_t n, int chunk, const float4* aos, int32_t* idx, float* d2) {
-  k_nn_search<G><<<blocks, NN_THREADS, 0, st>>>(g, q, rs, order, n, chunk, aos, idx, d2);
+// phase 2: one thread per far query, grid-stride over the queue
+__global__ void __launch_bounds__(NN_THREADS) k_nn_far(GridView g, const double* __restrict__ q, RadiusSrc rs,
+                                                       const float4* __restrict__ aos, int32_t* __restrict__ idx_out,
+                                                       float* __restrict__ d2_out, const FarItem* __restrict__ far,
+                                                       const unsigned int* __restrict__ far_count) {
+  const unsigned count = *far_count;
+  for (unsigned e = blockIdx.x * NN_THREADS + threadIdx.x; e < count; e += gridDim.x * NN_THREADS) {
+    const FarItem it = far[e];
+    double px, py, pz, R;
+    Query Q;
+    Q.load(g, q, rs, it.i, px, py, pz, R);
+    Q.best = it.best;
+    FarSearch F(g, Q);
+    F.run();
+    nn_write(Q.best, px, py, pz, R, aos, it.i, idx_out, d2_out);
+  }
 }
 
 int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, double fixed_radius,
@@ -313,9 +371,8 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   if (d_opt_num && !sweep) PCD_FAIL(ctx, PCD_E_INVALID, "opt_num given without a range sweep");
   const GridView& g = cloud->grid;
   const uint32_t* order = nullptr;
-  const char* genv = getenv("PCD_B200_NN_GROUP");   // tuning knob (tools/explore_nn.py)
-  const int group = genv ? atoi(genv) : 0;
-  int G = group ? group : g_nn_group;
+  const char* kenv = getenv("PCD_B200_NN_K1");      // tuning knobs (tools/explore_nn.py)
+  const int K1 = kenv ? atoi(kenv) : 1;
   if (n > 2048) {
     ProfScope ps(ctx, PCD_K_NN_KEYSORT, st);
     PCD_CUDA(ctx, ctx->keys.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->keys_alt.ensure(4 * (size_t)n));
@@ -334,22 +391,20 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   RadiusSrc rs;
   rs.radius = d_radius; rs.opt_num = d_opt_num; rs.fixed = fixed_radius;
   rs.max_r = sweep ? sweep->max_r : 0; rs.min_r = sweep ? sweep->min_r : 0; rs.drop = sweep ? sweep->drop : 0;
-  const int gpc = NN_THREADS / G;
-  int64_t want = (n + (int64_t)ctx->sm_count * 8 - 1) / ((int64_t)ctx->sm_count * 8);
-  int chunk = (int)((want + gpc - 1) / gpc) * gpc;
-  if (chunk < gpc) chunk = gpc;
-  if (chunk > NN_MAX_CHUNK) chunk = NN_MAX_CHUNK;
-  int blocks = (int)((n + chunk - 1) / chunk);
+  PCD_CUDA(ctx, ctx->far_q.ensure(sizeof(FarItem) * (size_t)n + 16));
+  unsigned int* far_count = ctx->far_q.as<unsigned int>();
+  FarItem* far = (FarItem*)(ctx->far_q.as<char>() + 16);
   const float4* aos = (const float4*)cloud->aos;
+  const int blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
   ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
-  switch (G) {
-    case 1: launch_nn<1>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
-    case 2: launch_nn<2>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
-    case 4: launch_nn<4>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
-    case 16: launch_nn<16>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
-    case 32: launch_nn<32>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
-    default: launch_nn<8>(blocks, st, g, d_q, rs, order, n, chunk, aos, d_idx, d2); break;
-  }
+  PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 4, st));
+  if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, d_q, rs, order, n, aos, d_idx, d2, far, far_count);
+  else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, d_q, rs, order, n, aos, d_idx, d2, far, far_count);
+  PCD_LAUNCH_CHECK(ctx);
+  int far_blocks = ctx->sm_count * 8;
+  if ((int64_t)far_blocks * NN_THREADS > n) far_blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
+  ProfScope psf(ctx, PCD_K_NN_FAR, st);
+  k_nn_far<<<far_blocks, NN_THREADS, 0, st>>>(g, d_q, rs, aos, d_idx, d2, far, far_count);
   PCD_LAUNCH_CHECK(ctx);
   ctx->counters[0] += n;
   return PCD_OK;

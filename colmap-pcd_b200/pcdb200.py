@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpcd_b200.so")
 
-K_NN_KEYSORT, K_NN_SEARCH, K_ASSOC_RECORD, K_RESJAC, K_PROJECT = 0, 1, 2, 3, 4
+K_NN_KEYSORT, K_NN_SEARCH, K_ASSOC_RECORD, K_RESJAC, K_PROJECT, K_NN_FAR = 0, 1, 2, 3, 4, 5
 TYPE_PROJ, TYPE_ICP, TYPE_ICP_GROUND, TYPE_NONE = 0, 1, 2, 255
 ASSOC_LOCAL, ASSOC_GLOBAL, ASSOC_WHOLE_MAP = 0, 1, 2
 

@@ -83,6 +83,7 @@ enum {
   PCD_K_ASSOC_RECORD = 2, /* k_assoc_record                                     */
   PCD_K_RESJAC = 3,       /* k_resjac (+ partial-sum reduction)                 */
   PCD_K_PROJECT = 4,      /* k_project (z-buffer splat)                         */
+  PCD_K_NN_FAR = 5,       /* k_nn_far (far queries; also inside PCD_K_NN_SEARCH) */
   PCD_K_COUNT = 8
 };
 PCD_API int pcd_ctx_profile(pcd_ctx* ctx, int enable);
