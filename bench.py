@@ -312,7 +312,7 @@ def run_b200(args):
     barrier()
     gpu_ms = sum(a.elapsed_time(b) for a, b in evs)
     launches = ctx.launches - launches0
-    ktime = {k: ctx.kernel_time(getattr(pcd, k)) for k in ("K_NN_KEYSORT", "K_NN_SEARCH", "K_ASSOC_RECORD", "K_RESJAC")}
+    ktime = {k: ctx.kernel_time(getattr(pcd, k)) for k in ("K_NN_KEYSORT", "K_NN_SEARCH", "K_NN_FAR", "K_ASSOC_RECORD", "K_RESJAC")}
     ctx.profile(False)
     accepted = int(o["accepted"].sum().item())
     # the path's one exchange: sum r^2 and counters over ranks (r is NaN-free: w = 0 rows give r = 0)
@@ -364,7 +364,7 @@ def run_b200(args):
                      "e2e": {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
                              "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                              "api": "pcd_associate_batch + pcd_weights_from_type + pcd_residual_jacobian_batch (host pointers, pinned)"},
-                     "roofline": {"bound": "hbm", "kernel": "k_nn_search", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "roofline": {"bound": "hbm", "kernel": "k_nn_search + k_nn_far (timed together)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                   "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                                   "algorithmic_bytes_per_query": ALG_BYTES_NN, "queries_per_launch": Q,
                                   "avg_launch_ms": 1e3 * nn_avg_s, "launches_timed": int(nn_n)},

@@ -278,6 +278,7 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
 
   int xsub = 4;                                  // x cells per (y, z) cell edge; power of two
   if (const char* e = getenv("PCD_B200_XSUB")) { int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) xsub = v; }
+  const bool auto_mode = !(cell_size > 0.0f);
   auto setup = [&](float cs) -> bool {   // fills G dims for cell edge cs; false if too many cells
     G.c = cs; G.inv_c = 1.0f / cs;
     G.xs = xsub; G.cx = cs / (float)xsub; G.inv_cx = G.inv_c * (float)xsub;
@@ -285,6 +286,7 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
     double dims[3];
     for (int d = 0; d < 3; d++) dims[d] = floor((double)(c->bb_hi[d] - c->bb_lo[d]) * (d == 0 ? G.inv_cx : G.inv_c)) + 1.0;
     double total = dims[0] * dims[1] * dims[2];
+    if (auto_mode && total > fmax(6.4e7, 24.0 * (double)n)) return false;      // keep the cell table near the cloud's size
     if (total > 2.0e9 || dims[0] > 2.0e6 || dims[1] > 2.0e6 || dims[2] > 2.0e6) return false;
     G.dx = (int)dims[0]; G.dy = (int)dims[1]; G.dz = (int)dims[2];
     c->n_cells = (int64_t)G.dx * G.dy * G.dz;
@@ -318,7 +320,7 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
     int rc = sort_keys(); if (rc) return rc;
   } else {
     // density-driven: aim for target_occ points per occupied cell (power-of-two steps)
-    double lo_occ = 6.0, hi_occ = 24.0;
+    double lo_occ = 12.0, hi_occ = 48.0;
     if (const char* e = getenv("PCD_B200_OCC_LO")) lo_occ = atof(e);
     if (const char* e = getenv("PCD_B200_OCC_HI")) hi_occ = atof(e);
     cs = 0.125f;

@@ -2,22 +2,21 @@
 // src/lidar/kdtree.cc:10-21; float32 L2 in FLANN's L2_Simple order (dx2+dy2)+dz2 on the
 // float-cast query, src/lidar/ply.cc:92; ties -> lowest original index).
 //
-// Pipeline per batch:  k_query_keys -> cub radix sort (cell id, query id) -> k_nn_search.
+// Pipeline per batch:  k_query_keys -> cub radix sort (cell id, query id) -> k_nn_search -> k_nn_far.
 // The grid is anisotropic: cells are c x c in (y, z) and c / xs along x.  A (y, z) row of cells
 // is ONE contiguous range of the cell-sorted points, so any x interval of a row costs two
 // cell_start loads, and the finer x resolution only narrows the interval that is scanned.
 //
-// k_nn_search, one CTA per contiguous chunk of the cell-sorted queries (neighbouring queries
-// share cells, so their candidate loads hit the same L1 lines / sectors):
-//   phase 1: ONE THREAD PER QUERY.  Own cell first (gives a distance bound), then the rows of the
-//            (2*K1+1)^2 (y, z) neighbourhood in order of increasing distance; a row is skipped when
-//            its distance lower bound exceeds the current best, and its x interval is clipped to
-//            the chord of the current best-distance ball.
-//   phase 2: the few queries the K1 block could not certify (best distance > distance to the
-//            block faces: outliers far from every surface) are compacted in shared memory and
-//            handled one WARP per query, best-first over the occupancy words of 4x4x4-cell blocks:
-//            empty space costs one 8-byte load per 64 cells, and only cells whose box distance
-//            beats the current best are ever scanned.
+// k_nn_search: ONE THREAD PER QUERY, queries in cell-sorted order (neighbouring threads share
+//   cells, so their candidate loads hit the same L1 lines / sectors).  Own cell first (gives a
+//   distance bound), then the rows of the (2*K1+1)^2 (y, z) neighbourhood in order of increasing
+//   distance; a row is skipped when its distance lower bound exceeds the current best, and its x
+//   interval is clipped to the chord of the current best-distance ball.  Queries the K1 block
+//   cannot certify (best distance > distance to the block faces: outliers far from every
+//   surface) are pushed, warp-aggregated, to a device queue.
+// k_nn_far: one thread per queued query, best-first over the occupancy words of 4x4x4-cell
+//   blocks in Chebyshev shells: empty space costs one 8-byte load per 64 cells, and only cells
+//   whose box distance beats the current best are ever scanned.
 // Exactness: a row / interval is skipped only when a conservative lower bound on its distance
 // (cell geometry minus a float-rounding margin) exceeds the current best, so every point that
 // could win or tie is examined; the winner is min over (d2 bits << 32 | original index).
@@ -56,6 +55,9 @@ __global__ void k_query_keys(const double* __restrict__ q, int64_t n, GridView g
 }
 
 constexpr int NN_THREADS = 256;
+#ifndef NN_MIN_BLOCKS
+#define NN_MIN_BLOCKS 5
+#endif
 constexpr float SHRINK = 0.999999f;   // applied to lower bounds before comparing with a float d2
 constexpr float GROW = 1.000001f;
 
@@ -315,7 +317,7 @@ __device__ __forceinline__ void nn_write(unsigned long long best, double px, dou
 struct FarItem { unsigned long long best; uint32_t i; uint32_t pad; };
 
 template <int K1>
-__global__ void __launch_bounds__(NN_THREADS) k_nn_search(GridView g, const double* __restrict__ q, RadiusSrc rs,
+__global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridView g, const double* __restrict__ q, RadiusSrc rs,
                                                           const uint32_t* __restrict__ order, int64_t n,
                                                           const float4* __restrict__ aos, int32_t* __restrict__ idx_out,
                                                           float* __restrict__ d2_out, FarItem* __restrict__ far,
