@@ -119,6 +119,10 @@ def load_mods():
     return pcd, synth
 
 
+def load_shard():
+    return entry._load("pcd_shard", os.path.join(entry.PKG, "shard.py"))
+
+
 def load_oracle():
     """The CPU checker / baseline.  bench.py may execute it ONLY for cpu_baseline and --impl reference."""
     return entry._load("orc", os.path.join(ROOT, "oracle", "orc.py"))
@@ -140,7 +144,9 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
             "config": {"workload": f"{args.workload}: {desc}", "cloud_points": n_cloud, "queries_per_gpu": q_per_gpu,
                        "queries_total": q_per_gpu * world, "radius_sweep": list(SWEEP), "variant": "global (incremental_mapper.cc:1430-1468)",
                        "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
-                       "parallelism": f"queries sharded x{world}, cloud+index replicated"}}
+                       "parallelism": f"queries sharded x{world}, cloud+index replicated",
+                       "exchange": "none (1 GPU)" if world == 1 else
+                       "per pass: all_gather of [r|J] fp64 blocks (32 B/query) on a side stream + all_reduce of sum r^2, NCCL"}}
 
 
 def cpu_pass(orc, tree, q, rng, threads):
@@ -276,6 +282,11 @@ def run_b200(args):
     d_r = torch.empty(Q, dtype=torch.float64, device=dev)
     d_J = torch.empty((Q, 3), dtype=torch.float64, device=dev)
     d_sum = torch.zeros(3, dtype=torch.float64, device=dev)
+    # [r | Jx Jy Jz] blocks, double-buffered so that the gather of pass k overlaps the kernels of pass k+1
+    d_rJ = [torch.empty((Q, 4), dtype=torch.float64, device=dev) for _ in range(2)]
+    shard = load_shard()
+    gather = shard.BlockGather(Q, dev) if world > 1 else None
+    step_no = [0]
     flush = None if Q * 24 > 126e6 * 2 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
 
@@ -284,8 +295,19 @@ def run_b200(args):
         ctx.weights_from_type_dev(o["type"].data_ptr(), Q, *WEIGHTS, d_w.data_ptr(), stream)
         ctx.residual_jacobian_dev(d_q.data_ptr(), o["abcd"].data_ptr(), d_w.data_ptr(), Q, d_r.data_ptr(), d_J.data_ptr(),
                                   d_sum.data_ptr(), stream)
+        if world > 1:
+            # the path's one exchange step: gather the Jacobian blocks and residuals over
+            # NCCL/NVLink on a side stream, all-reduce sum r^2 (d_sum[0]) with it
+            blk = d_rJ[step_no[0] & 1]
+            step_no[0] += 1
+            gather.wait()                       # the previous pass's gather must have drained `out`
+            blk[:, 0].copy_(d_r); blk[:, 1:4].copy_(d_J)
+            gather.start(blk)
+            dist.all_reduce(d_sum, op=dist.ReduceOp.SUM)
 
     def barrier():
+        if gather is not None:
+            gather.wait()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -309,8 +331,11 @@ def run_b200(args):
         b.record()
         if flush is not None:
             flush.fill_(1)
+    if gather is not None:                      # the last pass's gather belongs to the timed region
+        gather.wait()
+    ev_end = torch.cuda.Event(enable_timing=True); ev_end.record()
     barrier()
-    gpu_ms = sum(a.elapsed_time(b) for a, b in evs)
+    gpu_ms = evs[0][0].elapsed_time(ev_end) if flush is None else sum(a.elapsed_time(b) for a, b in evs)
     launches = ctx.launches - launches0
     ktime = {k: ctx.kernel_time(getattr(pcd, k)) for k in ("K_NN_KEYSORT", "K_NN_SEARCH", "K_NN_FAR", "K_ASSOC_RECORD", "K_RESJAC")}
     ctx.profile(False)
