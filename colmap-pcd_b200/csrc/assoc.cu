@@ -11,6 +11,7 @@
 // -fmad=false so no product-sum is contracted.
 #include "nn.cuh"
 #include <math.h>
+#include <vector>
 
 namespace pcd {
 
@@ -136,6 +137,68 @@ __global__ void k_match_proj(const double* __restrict__ p, const double* __restr
   if (angle_out) angle_out[i] = ang;
 }
 
+// Fused a18 + a19 for the end-to-end pass: weight by type (src/optim/bundle_adjustment.cc:1013-1028) and the
+// Jet<double,3> evaluation of the cost function (src/base/cost_functions.h:226-229) at the SfM point itself,
+// for ACCEPTED matches; a rejected query has no residual block in the reference and reports r = 0, J = 0.
+// Same operation order as k_resjac (resjac.cu).  partial: per-block sum of r^2 (fixed tree).
+__global__ void __launch_bounds__(256) k_assoc_eval(const double* __restrict__ p, const double* __restrict__ abcd,
+                                                    const uint8_t* __restrict__ accepted, const uint8_t* __restrict__ type,
+                                                    int64_t n, double wp, double wi, double wg, double* __restrict__ r_out,
+                                                    double* __restrict__ J_out, double* __restrict__ partial) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  double rr = 0.0;
+  if (i < n) {
+    double J[3] = {0.0, 0.0, 0.0};
+    if (accepted[i]) {
+      const uint8_t t = type[i];
+      const double w = t == PCD_TYPE_PROJ ? wp : (t == PCD_TYPE_ICP ? wi : (t == PCD_TYPE_ICP_GROUND ? wg : 0.0));
+      const double a = abcd[4 * i], b = abcd[4 * i + 1], c = abcd[4 * i + 2], d = abcd[4 * i + 3];
+      double s = ((p[3 * i] * a + p[3 * i + 1] * b) + p[3 * i + 2] * c) + d;
+      double u = 0.0 - s;
+      double f = u * u;
+      double sq = sqrt(f);
+      double inv = 1.0 / (2.0 * sq);
+      rr = w * sq;
+      const double nn[3] = {a, b, c};
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        double du = 0.0 - nn[k];
+        double fv = u * du + du * u;
+        J[k] = w * (fv * inv) + 0.0 * sq;
+      }
+    }
+    r_out[i] = rr;
+    if (J_out) { J_out[3 * i] = J[0]; J_out[3 * i + 1] = J[1]; J_out[3 * i + 2] = J[2]; }
+  }
+  if (partial) {
+    double s2 = rr * rr;
+    for (int o = 16; o > 0; o >>= 1) s2 += __shfl_down_sync(0xffffffffu, s2, o);
+    __shared__ double sh[8];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int k = 0; k < 8; k++) t += sh[k];
+      partial[blockIdx.x] = t;
+    }
+  }
+}
+
+__global__ void k_sum_blocks(const double* __restrict__ partial, int nb, double* __restrict__ out) {
+  __shared__ double sh[256];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < nb; i += 256) s += partial[i];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = sh[0];
+}
+
+struct EvalArgs { double wp, wi, wg; double* r; double* J; double* sum_sq; };
+
 }  // namespace pcd
 
 extern "C" {
@@ -164,22 +227,25 @@ int pcd_associate_batch_dev(pcd_cloud* cloud, const double* d_p, const double* d
   return PCD_OK;
 }
 
-int pcd_associate_batch(pcd_cloud* cloud, const double* p, const double* range, const int32_t* opt_num,
-                        const pcd_range_sweep* sweep, int64_t n, int variant, const pcd_assoc_out* out) {
-  if (!cloud) return PCD_E_INVALID;
+static int associate_pipeline(pcd_cloud* cloud, const double* p, const double* range, const int32_t* opt_num,
+                              const pcd_range_sweep* sweep, int64_t n, int variant, const pcd_assoc_out* out,
+                              const pcd::EvalArgs* ev) {
   pcd_ctx* ctx = cloud->ctx;
-  if (n < 0 || !out || (n > 0 && !p) || variant < 0 || variant > 2) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_associate_batch: bad argument");
-  if (n == 0) return PCD_OK;
   DeviceGuard g(ctx->device);
   cudaStream_t st = ctx->stream;
   // Chunked pipeline: H2D of chunk k+1 and D2H of chunk k-1 overlap the kernels of chunk k.
   const int64_t CH = (int64_t)1 << 20;
-  const size_t per_in = 24 + 8 + 4, per_out = 4 + 1 + 1 + 3 + 24 + 32 + 8 + 8 + 16;
+  const size_t per_in = 24 + 8 + 4, per_out = 4 + 1 + 1 + 3 + 24 + 32 + 8 + 8 + 16 + (ev ? 8 + 24 + 1 : 0);
   for (int b = 0; b < 2; b++) {
     PCD_CUDA(ctx, ctx->stage_in[b].ensure(per_in * (size_t)(n < CH ? n : CH) + 64));
     PCD_CUDA(ctx, ctx->stage_out[b].ensure(per_out * (size_t)(n < CH ? n : CH) + 256));
   }
   int64_t nchunks = (n + CH - 1) / CH;
+  double* d_chunk_sums = nullptr;
+  if (ev && ev->sum_sq) {
+    PCD_CUDA(ctx, ctx->stage_aux[0].ensure(8 * (size_t)nchunks + 8 * (size_t)pcd_blocks(CH, 256) * 2));
+    d_chunk_sums = ctx->stage_aux[0].as<double>();
+  }
   for (int64_t c = 0; c < nchunks; c++) {
     int b = (int)(c & 1);
     int64_t lo = c * CH, m = (n - lo < CH) ? (n - lo) : CH;
@@ -198,17 +264,27 @@ int pcd_associate_batch(pcd_cloud* cloud, const double* p, const double* range, 
     pcd_assoc_out d = {};
     size_t off = 0;
     auto take = [&](size_t bytes) { char* q = dout + off; off += (bytes + 15) & ~(size_t)15; return q; };
-    d.abcd = out->abcd ? (double*)take(32 * (size_t)m) : nullptr;
+    d.abcd = (out->abcd || ev) ? (double*)take(32 * (size_t)m) : nullptr;
+    double* d_r = ev ? (double*)take(8 * (size_t)m) : nullptr;
+    double* d_J = (ev && ev->J) ? (double*)take(24 * (size_t)m) : nullptr;
     d.xyz = out->xyz ? (double*)take(24 * (size_t)m) : nullptr;
     d.dist = out->dist ? (double*)take(8 * (size_t)m) : nullptr;
     d.angle = out->angle ? (double*)take(8 * (size_t)m) : nullptr;
     d.idx = (int32_t*)take(4 * (size_t)m);
     d.rgb = out->rgb ? (uint8_t*)take(3 * (size_t)m) : nullptr;
-    d.accepted = out->accepted ? (uint8_t*)take((size_t)m) : nullptr;
-    d.type = out->type ? (uint8_t*)take((size_t)m) : nullptr;
+    d.accepted = (out->accepted || ev) ? (uint8_t*)take((size_t)m) : nullptr;
+    d.type = (out->type || ev) ? (uint8_t*)take((size_t)m) : nullptr;
     if (c >= 2) PCD_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev[4 + b], 0));             // D2H of chunk c-2 finished
     int rc = pcd_associate_batch_dev(cloud, d_p, d_range, d_on, sweep, m, variant, &d, st);
     if (rc) return rc;
+    if (ev) {
+      const int nb = pcd_blocks(m, 256);
+      double* part = d_chunk_sums ? d_chunk_sums + nchunks + (size_t)b * pcd_blocks(CH, 256) : nullptr;
+      pcd::ProfScope ps(ctx, PCD_K_RESJAC, st);
+      pcd::k_assoc_eval<<<nb, 256, 0, st>>>(d_p, d.abcd, d.accepted, d.type, m, ev->wp, ev->wi, ev->wg, d_r, d_J, part);
+      PCD_LAUNCH_CHECK(ctx);
+      if (part) { pcd::k_sum_blocks<<<1, 256, 0, st>>>(part, nb, d_chunk_sums + c); PCD_LAUNCH_CHECK(ctx); }
+    }
     PCD_CUDA(ctx, cudaEventRecord(ctx->ev[2 + b], st));
     PCD_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ctx->ev[2 + b], 0));
     cudaStream_t co = ctx->copy_out;
@@ -220,11 +296,43 @@ int pcd_associate_batch(pcd_cloud* cloud, const double* p, const double* range, 
     if (out->rgb) PCD_CUDA(ctx, cudaMemcpyAsync(out->rgb + 3 * lo, d.rgb, 3 * (size_t)m, cudaMemcpyDeviceToHost, co));
     if (out->accepted) PCD_CUDA(ctx, cudaMemcpyAsync(out->accepted + lo, d.accepted, (size_t)m, cudaMemcpyDeviceToHost, co));
     if (out->type) PCD_CUDA(ctx, cudaMemcpyAsync(out->type + lo, d.type, (size_t)m, cudaMemcpyDeviceToHost, co));
+    if (ev) {
+      PCD_CUDA(ctx, cudaMemcpyAsync(ev->r + lo, d_r, 8 * (size_t)m, cudaMemcpyDeviceToHost, co));
+      if (ev->J) PCD_CUDA(ctx, cudaMemcpyAsync(ev->J + 3 * lo, d_J, 24 * (size_t)m, cudaMemcpyDeviceToHost, co));
+    }
     PCD_CUDA(ctx, cudaEventRecord(ctx->ev[4 + b], co));
   }
   PCD_CUDA(ctx, cudaStreamSynchronize(ctx->copy_out));
   PCD_CUDA(ctx, cudaStreamSynchronize(st));
+  if (d_chunk_sums) {     // chunk sums added on the host in chunk order: deterministic
+    std::vector<double> hs((size_t)nchunks);
+    PCD_CUDA(ctx, cudaMemcpy(hs.data(), d_chunk_sums, 8 * (size_t)nchunks, cudaMemcpyDeviceToHost));
+    double t = 0.0;
+    for (double v : hs) t += v;
+    *ev->sum_sq = t;
+  }
   return PCD_OK;
+}
+
+int pcd_associate_batch(pcd_cloud* cloud, const double* p, const double* range, const int32_t* opt_num,
+                        const pcd_range_sweep* sweep, int64_t n, int variant, const pcd_assoc_out* out) {
+  if (!cloud) return PCD_E_INVALID;
+  pcd_ctx* ctx = cloud->ctx;
+  if (n < 0 || !out || (n > 0 && !p) || variant < 0 || variant > 2) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_associate_batch: bad argument");
+  if (n == 0) return PCD_OK;
+  return associate_pipeline(cloud, p, range, opt_num, sweep, n, variant, out, nullptr);
+}
+
+int pcd_associate_evaluate_batch(pcd_cloud* cloud, const double* p, const double* range, const int32_t* opt_num,
+                                 const pcd_range_sweep* sweep, int64_t n, int variant, double w_proj, double w_icp,
+                                 double w_ground, const pcd_assoc_out* out, double* r, double* J, double* sum_sq) {
+  if (!cloud) return PCD_E_INVALID;
+  pcd_ctx* ctx = cloud->ctx;
+  if (n < 0 || !out || (n > 0 && (!p || !r)) || variant < 0 || variant > 2)
+    PCD_FAIL(ctx, PCD_E_INVALID, "pcd_associate_evaluate_batch: bad argument");
+  if (n == 0) { if (sum_sq) *sum_sq = 0.0; return PCD_OK; }
+  pcd::EvalArgs ev = {w_proj, w_icp, w_ground, r, J, sum_sq};
+  return associate_pipeline(cloud, p, range, opt_num, sweep, n, variant, out, &ev);
 }
 
 int pcd_search_nn_batch(pcd_cloud* cloud, const double* q, int64_t n, double* l_pt, uint8_t* ok) {

@@ -14,9 +14,10 @@
 //   interval is clipped to the chord of the current best-distance ball.  Queries the K1 block
 //   cannot certify (best distance > distance to the block faces: outliers far from every
 //   surface) are pushed, warp-aggregated, to a device queue.
-// k_nn_far: one thread per queued query, best-first over the occupancy words of 4x4x4-cell
-//   blocks in Chebyshev shells: empty space costs one 8-byte load per 64 cells, and only cells
-//   whose box distance beats the current best are ever scanned.
+// k_nn_far: ONE WARP per queued query, best-first over the occupancy words of 4x4x4-cell blocks in
+//   Chebyshev shells: the blocks of a shell are spread over the lanes (empty space costs one 8-byte
+//   load per 64 cells), the cells of a block are bounded two per lane and a cell's points are scanned
+//   32 at a time; only cells whose box distance beats the warp's current best are ever scanned.
 // Exactness: a row / interval is skipped only when a conservative lower bound on its distance
 // (cell geometry minus a float-rounding margin) exceeds the current best, so every point that
 // could win or tie is examined; the winner is min over (d2 bits << 32 | original index).
@@ -199,13 +200,27 @@ struct Query {
   }
 };
 
-// ---- phase 2: far queries, one thread per query, best-first over the block occupancy words -----
+// ---- phase 2: far queries, ONE WARP per query, best-first over the block occupancy words -----------
+// Every lane holds the same query; the blocks of a Chebyshev shell are spread over the lanes (one
+// occupancy word each), occupied blocks that can still hold a winner are then visited by the whole warp:
+// the 64 cells of a block are bounded two per lane, and a cell's points are scanned 32 at a time with a
+// warp-wide min of (d2 bits << 32 | index) after every cell, so the pruning bound is always the warp's.
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long w = __shfl_xor_sync(0xffffffffu, v, o);
+    v = w < v ? w : v;
+  }
+  return v;
+}
+
 struct FarSearch {
   const GridView& g;
   Query& Q;
-  float b2;                  // min(R2, best distance so far)
+  const int lane;
+  float b2;                  // min(R2, best distance so far); warp-uniform
 
-  __device__ __forceinline__ FarSearch(const GridView& g_, Query& Q_) : g(g_), Q(Q_) { b2 = Q.bound2(); }
+  __device__ __forceinline__ FarSearch(const GridView& g_, Query& Q_, int lane_) : g(g_), Q(Q_), lane(lane_) { b2 = Q.bound2(); }
 
   // squared lower bound to cubic cell `bit` of block (X, Y, Z)
   __device__ __forceinline__ float cell_lb2(int X, int Y, int Z, int bit) const {
@@ -215,6 +230,15 @@ struct FarSearch {
     return (a * a + (b * b + c * c)) * SHRINK;
   }
 
+  // squared lower bound to the whole block (X, Y, Z)
+  __device__ __forceinline__ float block_lb2(int X, int Y, int Z) const {
+    const int sx = 4 * g.xs;
+    float a = Query::gap(Q.px, X * sx, X * sx + sx - 1, g.cx, g.margin), b = Query::gap(Q.py, 4 * Y, 4 * Y + 3, g.c, g.margin),
+          c = Query::gap(Q.pz, 4 * Z, 4 * Z + 3, g.c, g.margin);
+    return (a * a + (b * b + c * c)) * SHRINK;
+  }
+
+  // whole warp, uniform arguments: the points of one cubic cell, 32 at a time
   __device__ __forceinline__ void scan_cell(int X, int Y, int Z, int bit) {
     const int cxc = 4 * X + (bit & 3), cy = 4 * Y + ((bit >> 2) & 3), cz = 4 * Z + (bit >> 4);
     float gy = Query::gap(Q.py, cy, cy, g.c, g.margin), gz = Query::gap(Q.pz, cz, cz, g.c, g.margin);
@@ -224,71 +248,117 @@ struct FarSearch {
     if (!Q.chord(g, b2, g2, x0, x1)) return;
     const uint32_t lin = ((uint32_t)cz * (uint32_t)g.dy + (uint32_t)cy) * (uint32_t)g.dx;
     const uint32_t b = __ldg(&g.cell_start[lin + x0]), e = __ldg(&g.cell_start[lin + x1 + 1]);
-    Q.scan(g, b, e, 0, 1);
+    if (b == e) return;
+    Q.scan(g, b, e, lane, 32);
+    Q.best = warp_min_u64(Q.best);
     b2 = Q.bound2();
   }
 
-  // the occupied cells of one block: the nearest first (it usually brings the bound down to the true
-  // distance), then every other cell whose box distance still beats the bound
+  // whole warp, uniform arguments: the occupied cells of one block in order of increasing box distance
+  // (two cells per lane), stopping at the first cell that can no longer beat the warp's bound
   __device__ __forceinline__ void scan_block(int X, int Y, int Z, unsigned long long w) {
-    float best_lb = INFINITY; int best_bit = -1;
-    for (unsigned long long ww = w; ww; ww &= ww - 1) {
-      const int bit = __ffsll((long long)ww) - 1;
-      const float lb = cell_lb2(X, Y, Z, bit);
-      if (lb < best_lb || best_bit < 0) { best_lb = lb; best_bit = bit; }
+    unsigned key[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int bit = lane + 32 * h;
+      // lb >= 0, so its bit pattern orders like the value; the low 6 bits carry the cell (lb rounded DOWN: conservative)
+      key[h] = ((w >> bit) & 1ull) ? ((__float_as_uint(cell_lb2(X, Y, Z, bit)) & ~63u) | (unsigned)bit) : 0xffffffffu;
     }
-    if (best_bit < 0 || !(best_lb <= b2)) return;
-    scan_cell(X, Y, Z, best_bit);
-    for (unsigned long long ww = w & ~(1ull << best_bit); ww; ww &= ww - 1) {
-      const int bit = __ffsll((long long)ww) - 1;
-      if (cell_lb2(X, Y, Z, bit) <= b2) scan_cell(X, Y, Z, bit);
+    for (;;) {
+      unsigned k = min(key[0], key[1]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) k = min(k, __shfl_xor_sync(0xffffffffu, k, o));
+      if (k == 0xffffffffu || !(__uint_as_float(k & ~63u) <= b2)) return;
+      const int bit = (int)(k & 63u);
+      if (key[0] == k) key[0] = 0xffffffffu;
+      if (key[1] == k) key[1] = 0xffffffffu;
+      scan_cell(X, Y, Z, bit);
     }
   }
 
-  __device__ __forceinline__ void block(int X, int Y, int Z, float gyz2) {
+  // Each lane offers one candidate block (has == false: none).  The warp visits them in order of increasing
+  // box distance and stops at the first one that can no longer beat the bound.
+  __device__ __forceinline__ void visit(bool has, int X, int Y, int Z, unsigned long long w, float lb) {
+    unsigned key = has ? ((__float_as_uint(lb) & ~31u) | (unsigned)lane) : 0xffffffffu;
+    for (;;) {
+      unsigned k = key;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) k = min(k, __shfl_xor_sync(0xffffffffu, k, o));
+      if (k == 0xffffffffu || !(__uint_as_float(k & ~31u) <= b2)) return;
+      const int src = (int)(k & 31u);
+      if (lane == src) key = 0xffffffffu;
+      const int bX = __shfl_sync(0xffffffffu, X, src), bY = __shfl_sync(0xffffffffu, Y, src), bZ = __shfl_sync(0xffffffffu, Z, src);
+      const unsigned long long bw = __shfl_sync(0xffffffffu, w, src);
+      scan_block(bX, bY, bZ, bw);
+    }
+  }
+
+  // this lane's block: bound it and, if it can matter, fetch its occupancy word
+  __device__ __forceinline__ void offer(bool in_grid, int X, int Y, int Z) {
+    float lb = INFINITY;
+    unsigned long long w = 0;
+    if (in_grid) {
+      lb = block_lb2(X, Y, Z);
+      if (lb <= b2) w = __ldg(&g.occ[((int64_t)Z * g.nby + Y) * g.nbx + X]);
+    }
+    visit(w != 0, X, Y, Z, w, lb);
+  }
+
+  // one rectangle of blocks: axis `fix` (0 = x, 1 = y, 2 = z) held at `v`, the other two over [a0, a1] x [b0, b1]
+  // (a = the lower-numbered free axis).  Blocks are spread over the lanes, 32 at a time.
+  __device__ __forceinline__ void rect(int fix, int v, int a0, int a1, int b0, int b1) {
+    if (a0 > a1 || b0 > b1) return;
+    const int na = a1 - a0 + 1, total = na * (b1 - b0 + 1);
+    for (int base = 0; base < total; base += 32) {
+      const int t = base + lane;
+      const int a = a0 + t % na, b = b0 + t / na;
+      offer(t < total, fix == 0 ? v : a, fix == 1 ? v : (fix == 0 ? a : b), fix == 2 ? v : b);
+    }
+  }
+
+  // every point outside the cube of shell kb is at least sqrt(returned) away (faces on the grid boundary do not
+  // count); INFINITY when the cube covers the grid
+  __device__ __forceinline__ float certified2(int bx, int by, int bz, int kb) const {
     const int sx = 4 * g.xs;
-    float gx = Query::gap(Q.px, X * sx, X * sx + sx - 1, g.cx, g.margin);
-    if (!((gx * gx + gyz2) * SHRINK <= b2)) return;
-    const unsigned long long w = __ldg(&g.occ[((int64_t)Z * g.nby + Y) * g.nbx + X]);
-    if (w) scan_block(X, Y, Z, w);
+    float rc = INFINITY;
+    const int x0 = (bx - kb) * sx, x1 = (bx + kb + 1) * sx - 1, y0 = 4 * (by - kb), y1 = 4 * (by + kb) + 3,
+              z0 = 4 * (bz - kb), z1 = 4 * (bz + kb) + 3;
+    if (x0 > 0) rc = fminf(rc, Q.px - (float)x0 * g.cx);
+    if (x1 < g.dx - 1) rc = fminf(rc, (float)(x1 + 1) * g.cx - Q.px);
+    if (y0 > 0) rc = fminf(rc, Q.py - (float)y0 * g.c);
+    if (y1 < g.dy - 1) rc = fminf(rc, (float)(y1 + 1) * g.c - Q.py);
+    if (z0 > 0) rc = fminf(rc, Q.pz - (float)z0 * g.c);
+    if (z1 < g.dz - 1) rc = fminf(rc, (float)(z1 + 1) * g.c - Q.pz);
+    if (rc == INFINITY) return INFINITY;
+    rc = fmaxf(rc - g.margin, 0.0f);
+    return rc * rc * SHRINK;
   }
 
   __device__ __forceinline__ void run() {
     const int bx = (Q.ix / g.xs) >> 2, by = Q.iy >> 2, bz = Q.iz >> 2;
-    const int sx = 4 * g.xs;
+    // shells 0 and 1 together: the 27 blocks around the query's block, one per lane, nearest first
+    {
+      const int dz = lane / 9 - 1, dy = (lane / 3) % 3 - 1, dx = lane % 3 - 1;
+      const int X = bx + dx, Y = by + dy, Z = bz + dz;
+      offer(lane < 27 && X >= 0 && X < g.nbx && Y >= 0 && Y < g.nby && Z >= 0 && Z < g.nbz, X, Y, Z);
+    }
     const int kmax = max(g.nbx, max(g.nby, g.nbz));
-    for (int kb = 0; kb <= kmax; kb++) {
-      // the shell of blocks at Chebyshev distance kb, clamped to the grid
-      const int Z0 = max(bz - kb, 0), Z1 = min(bz + kb, g.nbz - 1), Y0 = max(by - kb, 0), Y1 = min(by + kb, g.nby - 1);
-      const int X0 = max(bx - kb, 0), X1 = min(bx + kb, g.nbx - 1);
-      for (int Z = Z0; Z <= Z1; Z++) {
-        const float gz = Query::gap(Q.pz, 4 * Z, 4 * Z + 3, g.c, g.margin);
-        if (!(gz * gz * SHRINK <= b2)) continue;
-        for (int Y = Y0; Y <= Y1; Y++) {
-          const float gy = Query::gap(Q.py, 4 * Y, 4 * Y + 3, g.c, g.margin);
-          const float gyz2 = gy * gy + gz * gz;
-          if (!(gyz2 * SHRINK <= b2)) continue;
-          if (abs(Z - bz) == kb || abs(Y - by) == kb) {
-            for (int X = X0; X <= X1; X++) block(X, Y, Z, gyz2);
-          } else {
-            if (bx - kb >= 0) block(bx - kb, Y, Z, gyz2);
-            if (bx + kb < g.nbx) block(bx + kb, Y, Z, gyz2);
-          }
-        }
+    for (int kb = 1; kb <= kmax; kb++) {
+      if (kb > 1) {
+        // the shell of blocks at Chebyshev distance kb, clamped to the grid: two z faces (full), two y faces
+        // (without the z-face rows), two x faces (without both)
+        const int Y0 = max(by - kb, 0), Y1 = min(by + kb, g.nby - 1), X0 = max(bx - kb, 0), X1 = min(bx + kb, g.nbx - 1);
+        const int Zi0 = max(bz - kb + 1, 0), Zi1 = min(bz + kb - 1, g.nbz - 1);      // z range without the z faces
+        const int Yi0 = max(by - kb + 1, 0), Yi1 = min(by + kb - 1, g.nby - 1);
+        if (bz - kb >= 0) rect(2, bz - kb, X0, X1, Y0, Y1);
+        if (bz + kb < g.nbz) rect(2, bz + kb, X0, X1, Y0, Y1);
+        if (by - kb >= 0) rect(1, by - kb, X0, X1, Zi0, Zi1);
+        if (by + kb < g.nby) rect(1, by + kb, X0, X1, Zi0, Zi1);
+        if (bx - kb >= 0) rect(0, bx - kb, Yi0, Yi1, Zi0, Zi1);
+        if (bx + kb < g.nbx) rect(0, bx + kb, Yi0, Yi1, Zi0, Zi1);
       }
-      // every point outside the cube of shell kb is at least this far (faces on the grid boundary do not count)
-      float rc = INFINITY;
-      const int x0 = (bx - kb) * sx, x1 = (bx + kb + 1) * sx - 1, y0 = 4 * (by - kb), y1 = 4 * (by + kb) + 3,
-                z0 = 4 * (bz - kb), z1 = 4 * (bz + kb) + 3;
-      if (x0 > 0) rc = fminf(rc, Q.px - (float)x0 * g.cx);
-      if (x1 < g.dx - 1) rc = fminf(rc, (float)(x1 + 1) * g.cx - Q.px);
-      if (y0 > 0) rc = fminf(rc, Q.py - (float)y0 * g.c);
-      if (y1 < g.dy - 1) rc = fminf(rc, (float)(y1 + 1) * g.c - Q.py);
-      if (z0 > 0) rc = fminf(rc, Q.pz - (float)z0 * g.c);
-      if (z1 < g.dz - 1) rc = fminf(rc, (float)(z1 + 1) * g.c - Q.pz);
-      if (rc == INFINITY) break;
-      rc = fmaxf(rc - g.margin, 0.0f);
-      if (b2 <= rc * rc * SHRINK) break;
+      const float rc2 = certified2(bx, by, bz, kb);
+      if (rc2 == INFINITY || b2 <= rc2) break;
     }
   }
 };
@@ -345,21 +415,23 @@ __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridVie
   }
 }
 
-// phase 2: one thread per far query, grid-stride over the queue
-__global__ void __launch_bounds__(NN_THREADS) k_nn_far(GridView g, const double* __restrict__ q, RadiusSrc rs,
+// phase 2: one warp per far query, grid-stride over the queue
+__global__ void __launch_bounds__(NN_THREADS, 3) k_nn_far(GridView g, const double* __restrict__ q, RadiusSrc rs,
                                                        const float4* __restrict__ aos, int32_t* __restrict__ idx_out,
                                                        float* __restrict__ d2_out, const FarItem* __restrict__ far,
                                                        const unsigned int* __restrict__ far_count) {
   const unsigned count = *far_count;
-  for (unsigned e = blockIdx.x * NN_THREADS + threadIdx.x; e < count; e += gridDim.x * NN_THREADS) {
+  const int lane = threadIdx.x & 31;
+  const unsigned warps = gridDim.x * (NN_THREADS / 32);
+  for (unsigned e = blockIdx.x * (NN_THREADS / 32) + (threadIdx.x >> 5); e < count; e += warps) {
     const FarItem it = far[e];
     double px, py, pz, R;
     Query Q;
     Q.load(g, q, rs, it.i, px, py, pz, R);
     Q.best = it.best;
-    FarSearch F(g, Q);
+    FarSearch F(g, Q, lane);
     F.run();
-    nn_write(Q.best, px, py, pz, R, aos, it.i, idx_out, d2_out);
+    if (lane == 0) nn_write(Q.best, px, py, pz, R, aos, it.i, idx_out, d2_out);
   }
 }
 
@@ -403,8 +475,8 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, d_q, rs, order, n, aos, d_idx, d2, far, far_count);
   else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, d_q, rs, order, n, aos, d_idx, d2, far, far_count);
   PCD_LAUNCH_CHECK(ctx);
-  int far_blocks = ctx->sm_count * 8;
-  if ((int64_t)far_blocks * NN_THREADS > n) far_blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
+  int far_blocks = ctx->sm_count * 8;                      // one warp per queued query, grid-stride
+  if ((int64_t)far_blocks * (NN_THREADS / 32) > n) far_blocks = (int)((n + NN_THREADS / 32 - 1) / (NN_THREADS / 32));
   ProfScope psf(ctx, PCD_K_NN_FAR, st);
   k_nn_far<<<far_blocks, NN_THREADS, 0, st>>>(g, d_q, rs, aos, d_idx, d2, far, far_count);
   PCD_LAUNCH_CHECK(ctx);

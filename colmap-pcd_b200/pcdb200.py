@@ -271,6 +271,28 @@ class Cloud:
                                                  C.c_int64(n), C.c_int(variant), C.byref(out)), "pcd_associate_batch")
         return res
 
+    def associate_evaluate(self, p, weights, range_=None, opt_num=None, sweep=None, variant=ASSOC_LOCAL, fields=None, out=None,
+                           out_rj=None, jac=True):
+        """pcd_associate_evaluate_batch: association records + (r, J, sum r^2) of the accepted matches in one
+        pipelined host-pointer pass.  weights = (w_proj, w_icp, w_ground).  Returns (records, r, J, sum_sq)."""
+        p = _f64(p, 3); n = len(p)
+        allf = ("idx", "accepted", "type", "rgb", "xyz", "abcd", "dist", "angle")
+        fields = allf if fields is None else fields
+        shapes = {"idx": ((n,), np.int32), "accepted": ((n,), np.uint8), "type": ((n,), np.uint8), "rgb": ((n, 3), np.uint8),
+                  "xyz": ((n, 3), np.float64), "abcd": ((n, 4), np.float64), "dist": ((n,), np.float64), "angle": ((n,), np.float64)}
+        res = out if out is not None else {f: np.empty(*shapes[f]) for f in fields}
+        o = AssocOut(*[res[f].ctypes.data if f in res else None for f in allf])
+        r = None if range_ is None else _f64(np.broadcast_to(range_, (n,))).ravel()
+        on = None if opt_num is None else np.ascontiguousarray(opt_num, dtype=np.int32)
+        sw = None if sweep is None else RangeSweep(*sweep)
+        rr, J = out_rj if out_rj is not None else (np.empty(n), np.empty((n, 3)) if jac else None)
+        s = C.c_double(0.0)
+        self.ctx.check(lib().pcd_associate_evaluate_batch(self._h, _ptr(p), _ptr(r), _ptr(on), C.byref(sw) if sw is not None else None,
+                                                          C.c_int64(n), C.c_int(variant), C.c_double(weights[0]), C.c_double(weights[1]),
+                                                          C.c_double(weights[2]), C.byref(o), _ptr(rr), _ptr(J), C.byref(s)),
+                       "pcd_associate_evaluate_batch")
+        return res, rr, J, s.value
+
     def associate_dev(self, d_p, d_range, d_opt_num, sweep, n, variant, out_ptrs, stream=0):
         """out_ptrs: dict field -> device pointer (int)."""
         allf = ("idx", "accepted", "type", "rgb", "xyz", "abcd", "dist", "angle")

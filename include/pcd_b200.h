@@ -160,6 +160,16 @@ PCD_API int pcd_associate_batch_dev(pcd_cloud* cloud, const double* d_p_xyz, con
                                     const int32_t* d_opt_num, const pcd_range_sweep* sweep,
                                     int64_t n, int variant, const pcd_assoc_out* d_out, void* stream);
 
+/* One pipelined pass for the end-to-end flow: pcd_associate_batch, then for every ACCEPTED match the weight by
+ * type (src/optim/bundle_adjustment.cc:1013-1028) and the cost function with its 1x3 Jacobian evaluated at the
+ * SfM point itself (src/base/cost_functions.h:204-232) -- what AddLidarToProblem + the first Ceres evaluation
+ * produce.  The SfM points cross PCIe once and the records never come back to be re-uploaded.
+ * r[n], J[3n] (may be NULL): 0 for queries without an accepted match; sum_sq (may be NULL) = sum r^2. */
+PCD_API int pcd_associate_evaluate_batch(pcd_cloud* cloud, const double* p_xyz, const double* range,
+                                         const int32_t* opt_num, const pcd_range_sweep* sweep, int64_t n, int variant,
+                                         double w_proj, double w_icp, double w_ground, const pcd_assoc_out* out,
+                                         double* r, double* J, double* sum_sq);
+
 /* MatchVariablePoint2LidarPoint (src/optim/bundle_adjustment.cc:288-350): per point, among its
  * candidates cand[cand_start[i] .. cand_start[i+1]) (6 doubles each, track order) choose min
  * |v.n|/(|n||v|); outputs a Proj record (dist = point-to-plane).  found: uint8[n]. */

@@ -194,6 +194,29 @@ def test_associate_multi_chunk_pipeline(scene, orc, pcd, ctx):
     assert np.array_equal(got["abcd"][acc], want["abcd"][acc])
 
 
+def test_associate_evaluate_fused_pass(scene, orc, pcd, ctx):
+    """pcd_associate_evaluate_batch == association + weights + cost function on the accepted matches; multi-chunk."""
+    rng_ = np.random.default_rng(5)
+    reps = 28                                   # 1.12 M queries: crosses the 1 Mi chunk boundary
+    q = np.tile(scene["q"], (reps, 1)) + rng_.normal(0, 1e-3, (reps * len(scene["q"]), 3))
+    on = np.tile(scene["opt_num"], reps)
+    W = (10.0, 1000.0, 10000.0)
+    rec, r, J, s = scene["cloud"].associate_evaluate(q, W, opt_num=on, sweep=(1.5, 0.2, 0.1), variant=pcd.ASSOC_GLOBAL)
+    want = scene["tree"].associate(q, orc.search_range(on), variant=1)
+    acc = want["accepted"].astype(bool)
+    assert np.array_equal(rec["accepted"].astype(bool), acc) and np.array_equal(rec["idx"][acc], want["idx"][acc])
+    assert _close(rec["abcd"][acc], want["abcd"][acc]) and _close(rec["dist"][acc], want["dist"][acc])
+    w = np.where(want["type"] == 2, W[2], W[1])
+    ro, Jo = orc.resjac(q[acc], want["abcd"][acc], w[acc])
+    assert _close(r[acc], ro) and _close(J[acc], Jo)
+    assert not r[~acc].any() and not J[~acc].any()          # no residual block for a rejected query
+    assert _close(s, float(np.sum(ro * ro)), 1e-9)
+    # and it equals the three separate calls
+    w3 = ctx.weights_from_type(rec["type"], *W) * rec["accepted"]
+    r3, J3, _ = ctx.residual_jacobian(q[acc], rec["abcd"][acc], w3[acc])
+    assert np.array_equal(r3, r[acc]) and np.array_equal(J3, J[acc], equal_nan=True)
+
+
 def test_match_proj(ctx, orc):
     rng = np.random.default_rng(11)
     n = 3000
