@@ -51,6 +51,18 @@ __global__ void k_assoc_record(const float4* __restrict__ aos, const double* __r
     double l[6];
     uint8_t type = PCD_TYPE_NONE; uint8_t r = 0, g = 0, b = 0;
     double abcd[4] = {0, 0, 0, 0}, dist = 0, angle = 0, lx = 0, ly = 0, lz = 0;
+    // The search kernels report the nearest point inside the float ball of the search range; the reference's
+    // own test |l - p| <= range (fp64, :398-400 and twins) decides here.  A nearest point beyond the range is
+    // reported exactly like "no neighbour" (idx -1, type NONE): the reference would find it and drop it.
+    double R = INFINITY;
+    if (variant == PCD_ASSOC_WHOLE_MAP) R = 2.0;
+    else if (range) R = range[i];
+    else if (opt_num) R = sweep_range(opt_num[i], sw.max_r, sw.min_r, sw.drop);
+    if (idx >= 0 && R != INFINITY) {
+      float4 a = __ldg(&aos[2 * (int64_t)idx]);
+      double vx = (double)a.x - px, vy = (double)a.y - py, vz = (double)a.z - pz;
+      if (norm3(vx, vy, vz) > R) idx = -1;
+    }
     if (widen(aos, idx, l)) {
       normalize_plane(l, abcd);
       lx = l[0]; ly = l[1]; lz = l[2];
@@ -66,7 +78,6 @@ __global__ void k_assoc_record(const float4* __restrict__ aos, const double* __r
         double d2plane = fabs((px * abcd[0] + (py * abcd[1] + pz * abcd[2])) + abcd[3]);   // ComputeDist
         ok = !(d2plane > 1 || d > 2);
       } else {
-        double R = range ? range[i] : (opt_num ? sweep_range(opt_num[i], sw.max_r, sw.min_r, sw.drop) : INFINITY);
         ok = !(d > R);
       }
       if (ok) {
@@ -217,7 +228,7 @@ int pcd_associate_batch_dev(pcd_cloud* cloud, const double* d_p, const double* d
   double fixed = variant == PCD_ASSOC_WHOLE_MAP ? 2.0 : INFINITY;
   const double* rr = variant == PCD_ASSOC_WHOLE_MAP ? nullptr : d_range;
   const int32_t* on = variant == PCD_ASSOC_WHOLE_MAP ? nullptr : (d_range ? nullptr : d_opt_num);
-  int rc = pcd::nn_search_dev(cloud, d_p, rr, fixed, on, sweep, n, d_idx, nullptr, st);
+  int rc = pcd::nn_search_dev(cloud, d_p, rr, fixed, on, sweep, n, d_idx, nullptr, false, st);   // k_assoc_record applies the fp64 range test
   if (rc) return rc;
   pcd_range_sweep sw = sweep ? *sweep : pcd_range_sweep{0, 0, 0};
   pcd_assoc_out o = *d_out; o.idx = nullptr;   // idx already written by the search (or private)
@@ -349,7 +360,7 @@ int pcd_search_nn_batch(pcd_cloud* cloud, const double* q, int64_t n, double* l_
   int32_t* d_idx = (int32_t*)(d_l + 6 * n);
   uint8_t* d_ok = (uint8_t*)(d_idx + n);
   PCD_CUDA(ctx, cudaMemcpyAsync(d_q, q, 24 * (size_t)n, cudaMemcpyHostToDevice, st));
-  int rc = pcd::nn_search_dev(cloud, d_q, nullptr, INFINITY, nullptr, nullptr, n, d_idx, nullptr, st);
+  int rc = pcd::nn_search_dev(cloud, d_q, nullptr, INFINITY, nullptr, nullptr, n, d_idx, nullptr, false, st);
   if (rc) return rc;
   pcd::k_search_nn_widen<<<pcd_blocks(n, 256), 256, 0, st>>>((const float4*)cloud->aos, d_idx, n, d_l, d_ok);
   PCD_LAUNCH_CHECK(ctx);

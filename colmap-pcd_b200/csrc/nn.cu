@@ -23,6 +23,8 @@
 // could win or tie is examined; the winner is min over (d2 bits << 32 | original index).
 #include "nn.cuh"
 #include <cub/cub.cuh>
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 #include <math.h>
 #include <stdlib.h>
 
@@ -43,21 +45,37 @@ __device__ __forceinline__ double query_radius(const RadiusSrc& rs, uint32_t i) 
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
 
-__global__ void k_query_keys(const double* __restrict__ q, int64_t n, GridView g, uint32_t* __restrict__ keys,
-                             uint32_t* __restrict__ vals) {
+// Query record used by the search kernels: the float-cast query (the reference's cast, ply.cc:92) and the
+// search radius rounded UP to float (INFINITY = unbounded, NaN = invalid radius).  Written in original
+// order with coalesced stores; the search gathers it through the sorted order, one aligned 16-byte
+// load per query instead of three doubles plus the radius source.
+__global__ void k_query_keys(const double* __restrict__ q, RadiusSrc rs, int64_t n, GridView g, uint32_t* __restrict__ keys,
+                             uint32_t* __restrict__ vals, float4* __restrict__ qrec) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   float x = (float)q[3 * i], y = (float)q[3 * i + 1], z = (float)q[3 * i + 2];
-  int cx = clampi((int)floorf((x - g.ox) * g.inv_cx), 0, g.dx - 1);
-  int cy = clampi((int)floorf((y - g.oy) * g.inv_c), 0, g.dy - 1);
-  int cz = clampi((int)floorf((z - g.oz) * g.inv_c), 0, g.dz - 1);
-  keys[i] = (uint32_t)(((int64_t)cz * g.dy + cy) * g.dx + cx);
-  vals[i] = (uint32_t)i;
+  const double R = query_radius(rs, (uint32_t)i);
+  float Rf = INFINITY;
+  if (R != INFINITY) Rf = (R < 0.0 || isnan(R)) ? __int_as_float(0x7fc00000) : __double2float_ru(R);
+  qrec[i] = make_float4(x, y, z, Rf);
+  if (keys) {
+    int cx = clampi((int)floorf((x - g.ox) * g.inv_cx), 0, g.dx - 1);
+    int cy = clampi((int)floorf((y - g.oy) * g.inv_c), 0, g.dy - 1);
+    int cz = clampi((int)floorf((z - g.oz) * g.inv_c), 0, g.dz - 1);
+    keys[i] = (uint32_t)(((int64_t)cz * g.dy + cy) * g.dx + cx);
+    vals[i] = (uint32_t)i;
+  }
 }
 
 constexpr int NN_THREADS = 256;
 #ifndef NN_MIN_BLOCKS
-#define NN_MIN_BLOCKS 5
+#define NN_MIN_BLOCKS 8
+#endif
+#ifndef FAR_MIN_BLOCKS
+#define FAR_MIN_BLOCKS 6
+#endif
+#ifndef FAR_GROUP
+#define FAR_GROUP 16      // lanes per far query (32, 16 or 8)
 #endif
 constexpr float SHRINK = 0.999999f;   // applied to lower bounds before comparing with a float d2
 constexpr float GROW = 1.000001f;
@@ -115,22 +133,16 @@ struct Query {
     return rc * rc * SHRINK;
   }
 
-  // loads query `i`, derives its cell, radius bound and validity
-  __device__ __forceinline__ bool load(const GridView& g, const double* __restrict__ q, const RadiusSrc& rs, uint32_t i,
-                                       double& dx, double& dy, double& dz, double& R) {
-    dx = q[3 * (int64_t)i]; dy = q[3 * (int64_t)i + 1]; dz = q[3 * (int64_t)i + 2];
-    R = query_radius(rs, i);
-    qx = (float)dx; qy = (float)dy; qz = (float)dz;
+  // loads the record of query `i`, derives its cell, radius bound and validity
+  __device__ __forceinline__ bool load(const GridView& g, const float4* __restrict__ qrec, uint32_t i) {
+    const float4 r = __ldg(&qrec[i]);
+    qx = r.x; qy = r.y; qz = r.z;
     px = qx - g.ox; py = qy - g.oy; pz = qz - g.oz;
     ix = clampi((int)floorf(px * g.inv_cx), 0, g.dx - 1);
     iy = clampi((int)floorf(py * g.inv_c), 0, g.dy - 1);
     iz = clampi((int)floorf(pz * g.inv_c), 0, g.dz - 1);
-    if (R == INFINITY) R2 = INFINITY;
-    else {
-      float Rf = __double2float_ru(fmax(R, 0.0));
-      R2 = __fmul_ru(Rf, Rf) * 1.00001f + 1e-12f;
-    }
-    bool valid = isfinite(qx) && isfinite(qy) && isfinite(qz) && !(R < 0.0) && !isnan(R) && g.n > 0;
+    R2 = r.w == INFINITY ? INFINITY : __fmul_ru(r.w, r.w) * 1.00001f + 1e-12f;     // conservative bound on radius^2
+    bool valid = isfinite(qx) && isfinite(qy) && isfinite(qz) && !isnan(r.w) && g.n > 0;
     if (valid && R2 != INFINITY) {
       // no cloud point can be within R of a query farther than R from the grid box
       float bx = gap(px, 0, g.dx - 1, g.cx, g.margin), by = gap(py, 0, g.dy - 1, g.c, g.margin),
@@ -200,27 +212,37 @@ struct Query {
   }
 };
 
-// ---- phase 2: far queries, ONE WARP per query, best-first over the block occupancy words -----------
-// Every lane holds the same query; the blocks of a Chebyshev shell are spread over the lanes (one
-// occupancy word each), occupied blocks that can still hold a winner are then visited by the whole warp:
-// the 64 cells of a block are bounded two per lane, and a cell's points are scanned 32 at a time with a
-// warp-wide min of (d2 bits << 32 | index) after every cell, so the pruning bound is always the warp's.
-__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const unsigned long long w = __shfl_xor_sync(0xffffffffu, v, o);
-    v = w < v ? w : v;
-  }
-  return v;
-}
-
+// ---- phase 2: far queries, one GROUP of FAR_GROUP lanes per query, best-first over the block occupancy words ----
+// Every lane of a group holds the same query; the blocks of a Chebyshev shell are spread over the lanes (one
+// occupancy word each), occupied blocks that can still hold a winner are then visited by the whole group in
+// order of increasing box distance: the 64 cells of a block are bounded 64 / FAR_GROUP per lane, and a cell's
+// points are scanned FAR_GROUP at a time with a group-wide min of (d2 bits << 32 | index) after every cell, so
+// the pruning bound is always the group's.  The kernel is bound by the latency of its dependent loads
+// (occupancy word -> cell_start -> points); FAR_GROUP < 32 puts several independent queries into one warp.
+template <int G>
 struct FarSearch {
   const GridView& g;
   Query& Q;
+  const cg::thread_block_tile<G>& tile;
   const int lane;
-  float b2;                  // min(R2, best distance so far); warp-uniform
+  float b2;                  // min(R2, best distance so far); group-uniform
 
-  __device__ __forceinline__ FarSearch(const GridView& g_, Query& Q_, int lane_) : g(g_), Q(Q_), lane(lane_) { b2 = Q.bound2(); }
+  __device__ __forceinline__ FarSearch(const GridView& g_, Query& Q_, const cg::thread_block_tile<G>& t)
+      : g(g_), Q(Q_), tile(t), lane((int)t.thread_rank()) { b2 = Q.bound2(); }
+
+  __device__ __forceinline__ unsigned min_u32(unsigned v) const {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) v = min(v, tile.shfl_xor(v, o));
+    return v;
+  }
+  __device__ __forceinline__ unsigned long long min_u64(unsigned long long v) const {
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+      const unsigned long long w = tile.shfl_xor(v, o);
+      v = w < v ? w : v;
+    }
+    return v;
+  }
 
   // squared lower bound to cubic cell `bit` of block (X, Y, Z)
   __device__ __forceinline__ float cell_lb2(int X, int Y, int Z, int bit) const {
@@ -238,7 +260,7 @@ struct FarSearch {
     return (a * a + (b * b + c * c)) * SHRINK;
   }
 
-  // whole warp, uniform arguments: the points of one cubic cell, 32 at a time
+  // whole group, uniform arguments: the points of one cubic cell, G at a time
   __device__ __forceinline__ void scan_cell(int X, int Y, int Z, int bit) {
     const int cxc = 4 * X + (bit & 3), cy = 4 * Y + ((bit >> 2) & 3), cz = 4 * Z + (bit >> 4);
     float gy = Query::gap(Q.py, cy, cy, g.c, g.margin), gz = Query::gap(Q.pz, cz, cz, g.c, g.margin);
@@ -249,46 +271,46 @@ struct FarSearch {
     const uint32_t lin = ((uint32_t)cz * (uint32_t)g.dy + (uint32_t)cy) * (uint32_t)g.dx;
     const uint32_t b = __ldg(&g.cell_start[lin + x0]), e = __ldg(&g.cell_start[lin + x1 + 1]);
     if (b == e) return;
-    Q.scan(g, b, e, lane, 32);
-    Q.best = warp_min_u64(Q.best);
+    Q.scan(g, b, e, lane, G);
+    Q.best = min_u64(Q.best);
     b2 = Q.bound2();
   }
 
-  // whole warp, uniform arguments: the occupied cells of one block in order of increasing box distance
-  // (two cells per lane), stopping at the first cell that can no longer beat the warp's bound
+  // whole group, uniform arguments: the occupied cells of one block in order of increasing box distance
+  // (64 / G cells per lane), stopping at the first cell that can no longer beat the group's bound
   __device__ __forceinline__ void scan_block(int X, int Y, int Z, unsigned long long w) {
-    unsigned key[2];
+    constexpr int H = 64 / G;
+    unsigned key[H];
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const int bit = lane + 32 * h;
+    for (int h = 0; h < H; h++) {
+      const int bit = lane + G * h;
       // lb >= 0, so its bit pattern orders like the value; the low 6 bits carry the cell (lb rounded DOWN: conservative)
       key[h] = ((w >> bit) & 1ull) ? ((__float_as_uint(cell_lb2(X, Y, Z, bit)) & ~63u) | (unsigned)bit) : 0xffffffffu;
     }
     for (;;) {
-      unsigned k = min(key[0], key[1]);
+      unsigned k = key[0];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) k = min(k, __shfl_xor_sync(0xffffffffu, k, o));
+      for (int h = 1; h < H; h++) k = min(k, key[h]);
+      k = min_u32(k);
       if (k == 0xffffffffu || !(__uint_as_float(k & ~63u) <= b2)) return;
       const int bit = (int)(k & 63u);
-      if (key[0] == k) key[0] = 0xffffffffu;
-      if (key[1] == k) key[1] = 0xffffffffu;
+#pragma unroll
+      for (int h = 0; h < H; h++) if (key[h] == k) key[h] = 0xffffffffu;
       scan_cell(X, Y, Z, bit);
     }
   }
 
-  // Each lane offers one candidate block (has == false: none).  The warp visits them in order of increasing
+  // Each lane offers one candidate block (has == false: none).  The group visits them in order of increasing
   // box distance and stops at the first one that can no longer beat the bound.
   __device__ __forceinline__ void visit(bool has, int X, int Y, int Z, unsigned long long w, float lb) {
     unsigned key = has ? ((__float_as_uint(lb) & ~31u) | (unsigned)lane) : 0xffffffffu;
     for (;;) {
-      unsigned k = key;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) k = min(k, __shfl_xor_sync(0xffffffffu, k, o));
+      const unsigned k = min_u32(key);
       if (k == 0xffffffffu || !(__uint_as_float(k & ~31u) <= b2)) return;
       const int src = (int)(k & 31u);
       if (lane == src) key = 0xffffffffu;
-      const int bX = __shfl_sync(0xffffffffu, X, src), bY = __shfl_sync(0xffffffffu, Y, src), bZ = __shfl_sync(0xffffffffu, Z, src);
-      const unsigned long long bw = __shfl_sync(0xffffffffu, w, src);
+      const int bX = tile.shfl(X, src), bY = tile.shfl(Y, src), bZ = tile.shfl(Z, src);
+      const unsigned long long bw = tile.shfl(w, src);
       scan_block(bX, bY, bZ, bw);
     }
   }
@@ -305,11 +327,11 @@ struct FarSearch {
   }
 
   // one rectangle of blocks: axis `fix` (0 = x, 1 = y, 2 = z) held at `v`, the other two over [a0, a1] x [b0, b1]
-  // (a = the lower-numbered free axis).  Blocks are spread over the lanes, 32 at a time.
+  // (a = the lower-numbered free axis).  Blocks are spread over the lanes, G at a time.
   __device__ __forceinline__ void rect(int fix, int v, int a0, int a1, int b0, int b1) {
     if (a0 > a1 || b0 > b1) return;
     const int na = a1 - a0 + 1, total = na * (b1 - b0 + 1);
-    for (int base = 0; base < total; base += 32) {
+    for (int base = 0; base < total; base += G) {
       const int t = base + lane;
       const int a = a0 + t % na, b = b0 + t / na;
       offer(t < total, fix == 0 ? v : a, fix == 1 ? v : (fix == 0 ? a : b), fix == 2 ? v : b);
@@ -336,11 +358,15 @@ struct FarSearch {
 
   __device__ __forceinline__ void run() {
     const int bx = (Q.ix / g.xs) >> 2, by = Q.iy >> 2, bz = Q.iz >> 2;
-    // shells 0 and 1 together: the 27 blocks around the query's block, one per lane, nearest first
-    {
-      const int dz = lane / 9 - 1, dy = (lane / 3) % 3 - 1, dx = lane % 3 - 1;
+    // shells 0 and 1 together: the 27 blocks around the query's block, G at a time, nearest first within a
+    // round; the enumeration starts at the query's own block
+#pragma unroll
+    for (int base = 0; base < 27; base += G) {
+      const int t = base + lane;
+      const int u = t < 27 ? (t + 13) % 27 : 0;            // 13 = the query's own block
+      const int dz = u / 9 - 1, dy = (u / 3) % 3 - 1, dx = u % 3 - 1;
       const int X = bx + dx, Y = by + dy, Z = bz + dz;
-      offer(lane < 27 && X >= 0 && X < g.nbx && Y >= 0 && Y < g.nby && Z >= 0 && Z < g.nbz, X, Y, Z);
+      offer(t < 27 && X >= 0 && X < g.nbx && Y >= 0 && Y < g.nby && Z >= 0 && Z < g.nbz, X, Y, Z);
     }
     const int kmax = max(g.nbx, max(g.nby, g.nbz));
     for (int kb = 1; kb <= kmax; kb++) {
@@ -363,43 +389,50 @@ struct FarSearch {
   }
 };
 
-// final write: the reference's accept test |l - p| <= range in fp64 (src/optim/bundle_adjustment.cc:398-400,
-// Eigen's (a - b).norm() = sqrt(x2 + (y2 + z2))) decides whether a radius-bounded query reports a hit.
-__device__ __forceinline__ void nn_write(unsigned long long best, double px, double py, double pz, double R,
-                                         const float4* __restrict__ aos, uint32_t i, int32_t* __restrict__ idx_out,
+// The search reports the nearest point inside the conservative float ball.  The reference's accept test
+// |l - p| <= range in fp64 (src/optim/bundle_adjustment.cc:398-400, Eigen's (a - b).norm() = sqrt(x2 + (y2 + z2)))
+// is applied afterwards in ORIGINAL query order, where p, the radius and idx stream in coalesced: by
+// k_assoc_record on the association path, by k_nn_radius_filter for pcd_nn_batch with a radius.
+__device__ __forceinline__ void nn_write(unsigned long long best, uint32_t i, int32_t* __restrict__ idx_out,
                                          float* __restrict__ d2_out) {
   int32_t idx = -1; float d2 = INFINITY;
   if (best != ~0ull) {
     idx = (int32_t)(uint32_t)(best & 0xffffffffu);
     d2 = __uint_as_float((unsigned)(best >> 32));
-    if (R != INFINITY) {
-      float4 l = __ldg(&aos[2 * (int64_t)idx]);
-      double x = (double)l.x - px, y = (double)l.y - py, z = (double)l.z - pz;
-      double dist = sqrt(__dadd_rn(__dmul_rn(x, x), __dadd_rn(__dmul_rn(y, y), __dmul_rn(z, z))));
-      if (dist > R) { idx = -1; d2 = INFINITY; }
-    }
   }
   idx_out[i] = idx;
   if (d2_out) d2_out[i] = d2;
+}
+
+__global__ void k_nn_radius_filter(const double* __restrict__ q, RadiusSrc rs, int64_t n, const float4* __restrict__ aos,
+                                   int32_t* __restrict__ idx, float* __restrict__ d2) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t k = idx[i];
+  if (k < 0) return;
+  const double R = query_radius(rs, (uint32_t)i);
+  if (R == INFINITY) return;
+  const float4 l = __ldg(&aos[2 * (int64_t)k]);
+  const double x = (double)l.x - q[3 * i], y = (double)l.y - q[3 * i + 1], z = (double)l.z - q[3 * i + 2];
+  const double dist = sqrt(__dadd_rn(__dmul_rn(x, x), __dadd_rn(__dmul_rn(y, y), __dmul_rn(z, z))));
+  if (dist > R) { idx[i] = -1; if (d2) d2[i] = INFINITY; }
 }
 
 // phase 1: one thread per (cell-sorted) query; uncertified queries go to the far queue
 struct FarItem { unsigned long long best; uint32_t i; uint32_t pad; };
 
 template <int K1>
-__global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridView g, const double* __restrict__ q, RadiusSrc rs,
+__global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridView g, const float4* __restrict__ qrec,
                                                           const uint32_t* __restrict__ order, int64_t n,
-                                                          const float4* __restrict__ aos, int32_t* __restrict__ idx_out,
-                                                          float* __restrict__ d2_out, FarItem* __restrict__ far,
-                                                          unsigned int* __restrict__ far_count) {
+                                                          int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
+                                                          FarItem* __restrict__ far, unsigned int* __restrict__ far_count) {
   const int64_t slot = (int64_t)blockIdx.x * NN_THREADS + threadIdx.x;
   if (slot >= n) return;
-  double px, py, pz, R;
   const uint32_t i = order ? order[slot] : (uint32_t)slot;
   Query Q;
-  const bool valid = Q.load(g, q, rs, i, px, py, pz, R);
+  const bool valid = Q.load(g, qrec, i);
   const bool resolved = valid ? Q.search_block<K1>(g) : true;
-  if (resolved) nn_write(Q.best, px, py, pz, R, aos, i, idx_out, d2_out);
+  if (resolved) nn_write(Q.best, i, idx_out, d2_out);
   // warp-aggregated push of the uncertified queries
   const unsigned act = __activemask();
   const unsigned m = __ballot_sync(act, !resolved);
@@ -415,29 +448,28 @@ __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridVie
   }
 }
 
-// phase 2: one warp per far query, grid-stride over the queue
-__global__ void __launch_bounds__(NN_THREADS, 3) k_nn_far(GridView g, const double* __restrict__ q, RadiusSrc rs,
-                                                       const float4* __restrict__ aos, int32_t* __restrict__ idx_out,
-                                                       float* __restrict__ d2_out, const FarItem* __restrict__ far,
-                                                       const unsigned int* __restrict__ far_count) {
+// phase 2: one group of FAR_GROUP lanes per far query, grid-stride over the queue
+__global__ void __launch_bounds__(NN_THREADS, FAR_MIN_BLOCKS) k_nn_far(GridView g, const float4* __restrict__ qrec,
+                                                       int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
+                                                       const FarItem* __restrict__ far, const unsigned int* __restrict__ far_count) {
   const unsigned count = *far_count;
-  const int lane = threadIdx.x & 31;
-  const unsigned warps = gridDim.x * (NN_THREADS / 32);
-  for (unsigned e = blockIdx.x * (NN_THREADS / 32) + (threadIdx.x >> 5); e < count; e += warps) {
+  const cg::thread_block_tile<FAR_GROUP> tile = cg::tiled_partition<FAR_GROUP>(cg::this_thread_block());
+  constexpr unsigned per_block = NN_THREADS / FAR_GROUP;
+  const unsigned groups = gridDim.x * per_block;
+  for (unsigned e = blockIdx.x * per_block + threadIdx.x / FAR_GROUP; e < count; e += groups) {
     const FarItem it = far[e];
-    double px, py, pz, R;
     Query Q;
-    Q.load(g, q, rs, it.i, px, py, pz, R);
+    Q.load(g, qrec, it.i);
     Q.best = it.best;
-    FarSearch F(g, Q, lane);
+    FarSearch<FAR_GROUP> F(g, Q, tile);
     F.run();
-    if (lane == 0) nn_write(Q.best, px, py, pz, R, aos, it.i, idx_out, d2_out);
+    if (tile.thread_rank() == 0) nn_write(Q.best, it.i, idx_out, d2_out);
   }
 }
 
 int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, double fixed_radius,
                   const int32_t* d_opt_num, const pcd_range_sweep* sweep, int64_t n, int32_t* d_idx, float* d2,
-                  cudaStream_t st) {
+                  bool exact_radius, cudaStream_t st) {
   pcd_ctx* ctx = cloud->ctx;
   if (!cloud->has_index) PCD_FAIL(ctx, PCD_E_INVALID, "NN index not built (call pcd_index_build)");
   if (n == 0) return PCD_OK;
@@ -447,39 +479,51 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   const uint32_t* order = nullptr;
   const char* kenv = getenv("PCD_B200_NN_K1");      // tuning knobs (tools/explore_nn.py)
   const int K1 = kenv ? atoi(kenv) : 1;
-  if (n > 2048) {
-    ProfScope ps(ctx, PCD_K_NN_KEYSORT, st);
-    PCD_CUDA(ctx, ctx->keys.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->keys_alt.ensure(4 * (size_t)n));
-    PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->vals_alt.ensure(4 * (size_t)n));
-    cub::DoubleBuffer<uint32_t> kb(ctx->keys.as<uint32_t>(), ctx->keys_alt.as<uint32_t>());
-    cub::DoubleBuffer<uint32_t> vb(ctx->vals.as<uint32_t>(), ctx->vals_alt.as<uint32_t>());
-    k_query_keys<<<pcd_blocks(n, 256), 256, 0, st>>>(d_q, n, g, kb.Current(), vb.Current());
-    PCD_LAUNCH_CHECK(ctx);
-    int bits = 1; while (((int64_t)1 << bits) < cloud->n_cells && bits < 32) bits++;
-    size_t tmp = 0;
-    PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, kb, vb, (int)n, 0, bits, st));
-    PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
-    PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, kb, vb, (int)n, 0, bits, st));
-    order = vb.Current();
-  }
   RadiusSrc rs;
   rs.radius = d_radius; rs.opt_num = d_opt_num; rs.fixed = fixed_radius;
   rs.max_r = sweep ? sweep->max_r : 0; rs.min_r = sweep ? sweep->min_r : 0; rs.drop = sweep ? sweep->drop : 0;
+  PCD_CUDA(ctx, ctx->qrec.ensure(16 * (size_t)n));
+  float4* qrec = ctx->qrec.as<float4>();
+  {
+    ProfScope ps(ctx, PCD_K_NN_KEYSORT, st);
+    const bool sorted = n > 2048;
+    if (sorted) {
+      PCD_CUDA(ctx, ctx->keys.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->keys_alt.ensure(4 * (size_t)n));
+      PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->vals_alt.ensure(4 * (size_t)n));
+    }
+    cub::DoubleBuffer<uint32_t> kb(ctx->keys.as<uint32_t>(), ctx->keys_alt.as<uint32_t>());
+    cub::DoubleBuffer<uint32_t> vb(ctx->vals.as<uint32_t>(), ctx->vals_alt.as<uint32_t>());
+    k_query_keys<<<pcd_blocks(n, 256), 256, 0, st>>>(d_q, rs, n, g, sorted ? kb.Current() : nullptr, sorted ? vb.Current() : nullptr, qrec);
+    PCD_LAUNCH_CHECK(ctx);
+    if (sorted) {
+      int bits = 1; while (((int64_t)1 << bits) < cloud->n_cells && bits < 32) bits++;
+      size_t tmp = 0;
+      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, kb, vb, (int)n, 0, bits, st));
+      PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, kb, vb, (int)n, 0, bits, st));
+      order = vb.Current();
+    }
+  }
   PCD_CUDA(ctx, ctx->far_q.ensure(sizeof(FarItem) * (size_t)n + 16));
   unsigned int* far_count = ctx->far_q.as<unsigned int>();
   FarItem* far = (FarItem*)(ctx->far_q.as<char>() + 16);
-  const float4* aos = (const float4*)cloud->aos;
   const int blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
-  ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
-  PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 4, st));
-  if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, d_q, rs, order, n, aos, d_idx, d2, far, far_count);
-  else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, d_q, rs, order, n, aos, d_idx, d2, far, far_count);
-  PCD_LAUNCH_CHECK(ctx);
-  int far_blocks = ctx->sm_count * 8;                      // one warp per queued query, grid-stride
-  if ((int64_t)far_blocks * (NN_THREADS / 32) > n) far_blocks = (int)((n + NN_THREADS / 32 - 1) / (NN_THREADS / 32));
-  ProfScope psf(ctx, PCD_K_NN_FAR, st);
-  k_nn_far<<<far_blocks, NN_THREADS, 0, st>>>(g, d_q, rs, aos, d_idx, d2, far, far_count);
-  PCD_LAUNCH_CHECK(ctx);
+  {
+    ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
+    PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 4, st));
+    if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
+    else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
+    PCD_LAUNCH_CHECK(ctx);
+    int far_blocks = ctx->sm_count * 8;                      // one lane group per queued query, grid-stride
+    if ((int64_t)far_blocks * (NN_THREADS / FAR_GROUP) > n) far_blocks = (int)((n + NN_THREADS / FAR_GROUP - 1) / (NN_THREADS / FAR_GROUP));
+    ProfScope psf(ctx, PCD_K_NN_FAR, st);
+    k_nn_far<<<far_blocks, NN_THREADS, 0, st>>>(g, qrec, d_idx, d2, far, far_count);
+    PCD_LAUNCH_CHECK(ctx);
+  }
+  if (exact_radius && (d_radius || d_opt_num || fixed_radius != INFINITY)) {
+    k_nn_radius_filter<<<pcd_blocks(n, 256), 256, 0, st>>>(d_q, rs, n, (const float4*)cloud->aos, d_idx, d2);
+    PCD_LAUNCH_CHECK(ctx);
+  }
   ctx->counters[0] += n;
   return PCD_OK;
 }
@@ -493,7 +537,7 @@ int pcd_nn_batch_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius
   if (!cloud) return PCD_E_INVALID;
   if (n < 0 || (n > 0 && (!d_q || !d_idx))) PCD_FAIL(cloud->ctx, PCD_E_INVALID, "pcd_nn_batch_dev: bad argument");
   DeviceGuard g(cloud->ctx->device);
-  return pcd::nn_search_dev(cloud, d_q, d_radius, INFINITY, nullptr, nullptr, n, d_idx, d_d2, (cudaStream_t)stream);
+  return pcd::nn_search_dev(cloud, d_q, d_radius, INFINITY, nullptr, nullptr, n, d_idx, d_d2, true, (cudaStream_t)stream);
 }
 
 int pcd_nn_batch(pcd_cloud* cloud, const double* q, const double* radius, int64_t n, int32_t* idx, float* d2) {
@@ -512,7 +556,7 @@ int pcd_nn_batch(pcd_cloud* cloud, const double* q, const double* radius, int64_
   float* d_d2 = (float*)(d_idx + n);
   PCD_CUDA(ctx, cudaMemcpyAsync(d_q, q, 24 * (size_t)n, cudaMemcpyHostToDevice, st));
   if (radius) PCD_CUDA(ctx, cudaMemcpyAsync(d_r, radius, 8 * (size_t)n, cudaMemcpyHostToDevice, st));
-  int rc = pcd::nn_search_dev(cloud, d_q, d_r, INFINITY, nullptr, nullptr, n, d_idx, d_d2, st);
+  int rc = pcd::nn_search_dev(cloud, d_q, d_r, INFINITY, nullptr, nullptr, n, d_idx, d_d2, true, st);
   if (rc) return rc;
   if (idx) PCD_CUDA(ctx, cudaMemcpyAsync(idx, d_idx, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
   if (d2) PCD_CUDA(ctx, cudaMemcpyAsync(d2, d_d2, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));

@@ -35,33 +35,38 @@ d_idx = torch.empty(Q, dtype=torch.int32, device="cuda")
 d_d2 = torch.empty(Q, dtype=torch.float32, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
 ref = None
-for cell in cells:
-    for xs in xsubs:
-        os.environ["PCD_B200_XSUB"] = str(xs)
-        try:
-            info = cloud.build_index(cell)
-        except pcd.PcdError as e:
-            print(f"cell {cell} xs {xs}: {e}")
-            continue
-        for g in groups:
-            for ch in chunks:
-                os.environ["PCD_B200_NN_K1"] = str(g)
-                os.environ["PCD_B200_NN_CHUNK"] = str(ch)
-                rp = d_rad.data_ptr() if d_rad is not None else 0
-                for _ in range(2):
-                    cloud.nn_dev(d_q.data_ptr(), rp, Q, d_idx.data_ptr(), d_d2.data_ptr(), st)
-                torch.cuda.synchronize()
-                ctx.profile(True)
-                for _ in range(3):
-                    cloud.nn_dev(d_q.data_ptr(), rp, Q, d_idx.data_ptr(), d_d2.data_ptr(), st)
-                torch.cuda.synchronize()
-                ms, n = ctx.kernel_time(pcd.K_NN_SEARCH)
-                ks, _ = ctx.kernel_time(pcd.K_NN_KEYSORT)
-                fs, _ = ctx.kernel_time(pcd.K_NN_FAR)
-                ctx.profile(False)
-                res = d_idx.cpu().numpy()
-                if ref is None:
-                    ref = res
-                same = bool(np.array_equal(ref, res))
-                print(f"cell {cell:7.4f} xs {xs:2d} cells {info['n_cells']:>11d} K1 {g:2d} chunk {ch:4d}: search {ms / n:8.3f} ms  "
-                      f"(far {fs / n:6.3f}) keysort {ks / n:6.3f} ms  {Q / (ms / n) / 1e3:8.1f} Mq/s  hits {(res >= 0).mean():.3f} same={same}", flush=True)
+envs = [e for e in os.environ.get("EXPLORE_ENVS", "").split(";")] or [""]     # e.g. "PCD_B200_NN_FLAT=0;PCD_B200_NN_FLAT=1"
+for env in envs:
+  for kv in filter(None, env.split(",")):
+    os.environ[kv.split("=")[0]] = kv.split("=")[1]
+  print("env:", env or "(default)", flush=True)
+  for cell in cells:
+      for xs in xsubs:
+          os.environ["PCD_B200_XSUB"] = str(xs)
+          try:
+              info = cloud.build_index(cell)
+          except pcd.PcdError as e:
+              print(f"cell {cell} xs {xs}: {e}")
+              continue
+          for g in groups:
+              for ch in chunks:
+                  os.environ["PCD_B200_NN_K1"] = str(g)
+                  os.environ["PCD_B200_NN_CHUNK"] = str(ch)
+                  rp = d_rad.data_ptr() if d_rad is not None else 0
+                  for _ in range(2):
+                      cloud.nn_dev(d_q.data_ptr(), rp, Q, d_idx.data_ptr(), d_d2.data_ptr(), st)
+                  torch.cuda.synchronize()
+                  ctx.profile(True)
+                  for _ in range(3):
+                      cloud.nn_dev(d_q.data_ptr(), rp, Q, d_idx.data_ptr(), d_d2.data_ptr(), st)
+                  torch.cuda.synchronize()
+                  ms, n = ctx.kernel_time(pcd.K_NN_SEARCH)
+                  ks, _ = ctx.kernel_time(pcd.K_NN_KEYSORT)
+                  fs, _ = ctx.kernel_time(pcd.K_NN_FAR)
+                  ctx.profile(False)
+                  res = d_idx.cpu().numpy()
+                  if ref is None:
+                      ref = res
+                  same = bool(np.array_equal(ref, res))
+                  print(f"cell {cell:7.4f} xs {xs:2d} cells {info['n_cells']:>11d} K1 {g:2d} chunk {ch:4d}: search {ms / n:8.3f} ms  "
+                        f"(far {fs / n:6.3f}) keysort {ks / n:6.3f} ms  {Q / (ms / n) / 1e3:8.1f} Mq/s  hits {(res >= 0).mean():.3f} same={same}", flush=True)
