@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--cloud", type=int, default=0, help="override cloud size")
     ap.add_argument("--queries", type=int, default=0, help="override queries per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--zbuf-images", type=int, default=6, help="images per GPU of the depth-projection leg (0 = skip)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work of the cpu_baseline sample")
     return ap.parse_args()
 
@@ -146,7 +147,7 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
                        "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
                        "parallelism": f"queries sharded x{world}, cloud+index replicated",
                        "exchange": "none (1 GPU)" if world == 1 else
-                       "per pass: all_gather of [r|J] fp64 blocks (32 B/query) on a side stream + all_reduce of sum r^2, NCCL"}}
+                       "per pass: gather to rank 0 of r and J fp64 blocks (32 B/query) + all_reduce of sum r^2, NCCL on a side stream overlapping the next pass"}}
 
 
 def cpu_pass(orc, tree, q, rng, threads):
@@ -188,6 +189,40 @@ def cpu_baseline(orc, world_cloud, q, opt_num, seconds):
             "sample": f"{m} of the step's queries against the full cloud (association {ta:.2f} s + residual/Jacobian {tr:.2f} s); "
                       f"kd-tree build {build_s:.1f} s not included",
             "assoc_queries_per_s": m / ta, "resjac_evals_per_s": m / tr, "accepted_frac": float(rec["accepted"].mean())}, tree
+
+
+def zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, n_img, rank, world):
+    """Secondary metric (SURVEY.md 8d, configs[3]): depth projection of the resident cloud into this rank's images at
+    1920x1080, depth_image_scale 1.0, 3000 keypoints each -- PcdProj::SetNewImage through the host-pointer C ABI
+    (feature z-buffer, winners copied back), plus one dense z-buffer (the if_save_depth_image map)."""
+    opt = pcd.ProjOptions.default(depth_image_scale=1.0)
+    t0 = time.perf_counter()
+    cloud.build_submap(opt)
+    t_sub = time.perf_counter() - t0
+    shard = load_shard()
+    cams = synth.make_cameras(n_img * world, synth.scene_extent(n_cloud), cam=synth.OPENCV_1080)
+    mine = [cams[k] for k in shard.shard_images(len(cams), world, rank)]
+    imgs = [pcd.Image.make(c["qvec"], c["tvec"], c["cam"], c["width"], c["height"]) for c in mine]
+    coef = pcd.splat_coef(cams[0]["cam"], opt)
+    feats = synth.make_features(3000, cam=synth.OPENCV_1080)
+    fxy = np.concatenate([feats] * len(imgs)); fstart = np.arange(len(imgs) + 1, dtype=np.int64) * len(feats)
+    cloud.project_images(imgs[:1], coef, feats, fstart[:2])                      # warm-up
+    ctx.profile(True)
+    t0 = time.perf_counter()
+    widx, wr, stats = cloud.project_images(imgs, coef, fxy, fstart)
+    dt = time.perf_counter() - t0
+    k_ms, k_n = ctx.kernel_time(pcd.K_PROJECT)
+    ctx.profile(False)
+    t0 = time.perf_counter()
+    _, _, z, dstats = cloud.project_image(imgs[0], coef, None, dense=True)
+    dt_dense = time.perf_counter() - t0
+    return {"images": len(imgs), "image_size": [1920, 1080], "depth_image_scale": 1.0, "features_per_image": len(feats),
+            "submap_build_s": t_sub, "images_per_s": len(imgs) / dt, "point_projections_per_s": float(stats[1]) / dt,
+            "pixel_updates_per_s": float(stats[2]) / dt, "points_projected": int(stats[1]), "pixel_updates": int(stats[2]),
+            "features_hit": int(stats[3]), "k_project_ms_per_image": k_ms / max(k_n, 1),
+            "k_project_point_bytes_GBps": 16.0 * float(stats[1]) / max(k_ms * 1e-3, 1e-12) / 1e9,
+            "dense": {"seconds": dt_dense, "pixels_covered": int((z != np.iinfo(np.uint64).max).sum()),
+                      "pixel_atomics": int(dstats[2]), "pixel_atomics_per_s": float(dstats[2]) / dt_dense}}
 
 
 def run_reference(args):
@@ -282,10 +317,11 @@ def run_b200(args):
     d_r = torch.empty(Q, dtype=torch.float64, device=dev)
     d_J = torch.empty((Q, 3), dtype=torch.float64, device=dev)
     d_sum = torch.zeros(3, dtype=torch.float64, device=dev)
-    # [r | Jx Jy Jz] blocks, double-buffered so that the gather of pass k overlaps the kernels of pass k+1
-    d_rJ = [torch.empty((Q, 4), dtype=torch.float64, device=dev) for _ in range(2)]
+    # residual / Jacobian outputs are double-buffered so that the exchange of pass k overlaps the kernels of pass k+1
+    d_rb = [d_r, torch.empty_like(d_r)] if world > 1 else [d_r]
+    d_Jb = [d_J, torch.empty_like(d_J)] if world > 1 else [d_J]
     shard = load_shard()
-    gather = shard.BlockGather(Q, dev) if world > 1 else None
+    gather = shard.Exchange(Q, dev, root=0) if world > 1 else None
     step_no = [0]
     flush = None if Q * 24 > 126e6 * 2 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
@@ -293,17 +329,16 @@ def run_b200(args):
     def step():
         cloud.associate_dev(d_q.data_ptr(), 0, d_on.data_ptr(), SWEEP, Q, pcd.ASSOC_GLOBAL, optrs, stream)
         ctx.weights_from_type_dev(o["type"].data_ptr(), Q, *WEIGHTS, d_w.data_ptr(), stream)
-        ctx.residual_jacobian_dev(d_q.data_ptr(), o["abcd"].data_ptr(), d_w.data_ptr(), Q, d_r.data_ptr(), d_J.data_ptr(),
+        b = step_no[0] & 1 if world > 1 else 0
+        step_no[0] += 1
+        if world > 1:
+            gather.wait_buffer(b)               # the exchange of pass k-2 read these buffers
+        ctx.residual_jacobian_dev(d_q.data_ptr(), o["abcd"].data_ptr(), d_w.data_ptr(), Q, d_rb[b].data_ptr(), d_Jb[b].data_ptr(),
                                   d_sum.data_ptr(), stream)
         if world > 1:
-            # the path's one exchange step: gather the Jacobian blocks and residuals over
-            # NCCL/NVLink on a side stream, all-reduce sum r^2 (d_sum[0]) with it
-            blk = d_rJ[step_no[0] & 1]
-            step_no[0] += 1
-            gather.wait()                       # the previous pass's gather must have drained `out`
-            blk[:, 0].copy_(d_r); blk[:, 1:4].copy_(d_J)
-            gather.start(blk)
-            dist.all_reduce(d_sum, op=dist.ReduceOp.SUM)
+            # the path's one exchange step: all-gather of the residuals and Jacobian blocks and
+            # all-reduce of sum r^2, NCCL over NVLink on a side stream
+            gather.start(d_rb[b], d_Jb[b], d_sum, b)
 
     def barrier():
         if gather is not None:
@@ -341,7 +376,7 @@ def run_b200(args):
     ctx.profile(False)
     accepted = int(o["accepted"].sum().item())
     # the path's one exchange: sum r^2 and counters over ranks (r is NaN-free: w = 0 rows give r = 0)
-    red = torch.tensor([gpu_ms, float(accepted), float(torch.nansum(d_r * d_r).item())], dtype=torch.float64, device=dev)
+    red = torch.tensor([gpu_ms, float(accepted), float(torch.nansum(d_rb[(step_no[0] - 1) & 1 if world > 1 else 0] ** 2).item())], dtype=torch.float64, device=dev)
     mx = red.clone()
     if world > 1:
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -377,6 +412,13 @@ def run_b200(args):
     h2d = Q * (24 + 4)
     d2h = sum(int(np.prod(shapes[f][0])) * np.dtype(shapes[f][1]).itemsize for f in fields) + Q * (8 + 24) + 8 * ((Q + (1 << 20) - 1) >> 20)
 
+    zb = None
+    if args.zbuf_images > 0:
+        zb = zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, args.zbuf_images, rank, world)
+        if world > 1:
+            t = torch.tensor([zb["images_per_s"], zb["point_projections_per_s"], zb["pixel_updates_per_s"]], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            zb.update(images_per_s=float(t[0]), point_projections_per_s=float(t[1]), pixel_updates_per_s=float(t[2]), ranks=world)
     if rank == 0:
         ms_step = gpu_ms_max / args.steps
         line = base_line(args, n_cloud, Q, desc, world)
@@ -399,6 +441,8 @@ def run_b200(args):
                      "resjac_roofline_frac": ALG_BYTES_RESJAC * Q / (1e-3 * ktime["K_RESJAC"][0] / max(ktime["K_RESJAC"][1], 1)) / 1e9 / peak,
                      "accepted_frac": float(red[1].item()) / (Q * world), "sum_sq": float(red[2].item()),
                      "index": info, "setup_s": {"cloud_gen_and_replicate": t_gen, "upload_and_index_build": t_build}})
+        if zb is not None:
+            line["zbuffer"] = zb
         if world == 1 and not args.no_cpu_baseline:
             orc = load_oracle()
             cb, _ = cpu_baseline(orc, world_cloud, q_np, on_np, args.cpu_seconds)

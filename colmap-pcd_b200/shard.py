@@ -32,38 +32,67 @@ def reduce_stats(sum_sq, accepted, ground, group=None):
     return t
 
 
-class BlockGather:
-    """Gathers equal-sized per-rank [Q, 4] fp64 blocks (r | J) into one [world * Q, 4] tensor on every rank.
-    On CUDA the collective runs on its own stream so that it overlaps the next pass's kernels; wait()
-    makes the caller's stream depend on it."""
+class Exchange:
+    """The path's one exchange step per pass: all-gather of the per-rank residuals r [Q] and Jacobian blocks J [Q, 3]
+    (equal Q on every rank) and all-reduce (sum) of the fp64 statistics [sum r^2, accepted, ground].
 
-    def __init__(self, q_per_rank, device, group=None):
+    On CUDA everything runs on a side stream, so that the collectives of pass k overlap the kernels of pass k+1;
+    the caller alternates between two (r, J) output buffers and calls wait_buffer(b) before overwriting buffer b.
+    """
+
+    def __init__(self, q_per_rank, device, group=None, root=0):
+        """root = r: gather to rank r only (the consumer is the host-side solver of one process; the other ranks
+        send their 32 B/query once and receive nothing).  root = None: all-gather, every rank gets every block."""
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.group = group
-        self.out = torch.empty((self.world * q_per_rank, 4), dtype=torch.float64, device=device)
-        self.cuda = torch.device(device).type == "cuda"
-        self.stream = torch.cuda.Stream(device=device) if self.cuda else None
-        self.work = None
+        self.root = root
+        self.q = int(q_per_rank)
+        dev = torch.device(device)
+        self.cuda = dev.type == "cuda"
+        full = self.world * self.q if (root is None or self.rank == root) else 0
+        self.r_all = torch.empty(full, dtype=torch.float64, device=dev)
+        self.J_all = torch.empty((full, 3), dtype=torch.float64, device=dev)
+        self.stats = torch.zeros(3, dtype=torch.float64, device=dev)
+        self.stream = torch.cuda.Stream(device=dev) if self.cuda else None
+        self.events = [torch.cuda.Event() for _ in range(2)] if self.cuda else None
+        self.pending = [False, False]
 
-    def start(self, block):
-        if self.world == 1:
-            self.out.copy_(block)
-            return
-        if self.cuda:
-            self.stream.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(self.stream):
-                dist.all_gather_into_tensor(self.out, block, group=self.group)
+    def _run(self, r, J, stats):
+        if self.world > 1:
+            if self.root is None:
+                dist.all_gather_into_tensor(self.r_all, r, group=self.group)
+                dist.all_gather_into_tensor(self.J_all, J, group=self.group)
+            else:
+                here = self.rank == self.root
+                dist.gather(r, list(self.r_all.split(self.q)) if here else None, dst=self.root, group=self.group)
+                dist.gather(J, list(self.J_all.split(self.q)) if here else None, dst=self.root, group=self.group)
+            self.stats.copy_(stats)
+            dist.all_reduce(self.stats, op=dist.ReduceOp.SUM, group=self.group)
         else:
-            self.work = dist.all_gather_into_tensor(self.out, block, group=self.group, async_op=True)
+            self.r_all.copy_(r); self.J_all.copy_(J); self.stats.copy_(stats)
+
+    def start(self, r, J, stats, buf=0):
+        """r, J: this rank's outputs of the pass just enqueued; stats: fp64 [3]."""
+        if not self.cuda:
+            self._run(r, J, stats)
+            return
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.stream):
+            self._run(r, J, stats)
+            self.events[buf].record(self.stream)
+        self.pending[buf] = True
+
+    def wait_buffer(self, buf):
+        """Make the current stream wait until the exchange that read buffer `buf` has finished."""
+        if self.cuda and self.pending[buf]:
+            torch.cuda.current_stream().wait_event(self.events[buf])
+            self.pending[buf] = False
 
     def wait(self):
-        if self.world == 1:
-            return self.out
         if self.cuda:
             torch.cuda.current_stream().wait_stream(self.stream)
-        elif self.work is not None:
-            self.work.wait(); self.work = None
-        return self.out
+        return self.r_all, self.J_all, self.stats
 
 
 def gather_ragged(local, group=None):

@@ -84,6 +84,13 @@ def make_cloud(n, seed=SEED0, density=400.0, bad_frac=1e-3, lidar_frame=True, ch
     return out, dict(L=L, W=W, n_build=n_build)
 
 
+def scene_extent(n, density=400.0):
+    """L, W of the ground rectangle make_cloud(n) lays out (enough for make_cameras on ranks that did not generate)."""
+    total_area = n / density
+    L = float(np.sqrt(total_area * 0.5 / 0.75))
+    return dict(L=L, W=0.75 * L)
+
+
 def make_queries(world_cloud, q, seed=SEED0 + 1, sigma=0.10, outlier_frac=0.05):
     """SfM points: cloud points displaced by N(0, sigma^2 I); outlier_frac of them anywhere in a
     3 m ball instead.  Returns (p float64 [q,3], opt_num int32 [q] ~ U{0..15}), in hash order."""

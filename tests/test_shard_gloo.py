@@ -35,13 +35,23 @@ def _worker(rank, world, port, n_q, out_dir):
     r, J = orc.resjac(q[lo:hi], rec["abcd"], w)
     r = np.nan_to_num(r); J = np.nan_to_num(J)
     block = torch.from_numpy(np.concatenate([r[:, None], J], 1))
-    stats = shard.reduce_stats(float((r * r).sum()), int(rec["accepted"].sum()), int((rec["type"][rec["accepted"] > 0] == 2).sum()))
-    if n_q % world == 0:
-        g = shard.BlockGather(hi - lo, "cpu")
-        g.start(block)
-        allb = g.wait().clone()
-    else:
+    local = torch.tensor([float((r * r).sum()), float(rec["accepted"].sum()), float((rec["type"][rec["accepted"] > 0] == 2).sum())],
+                         dtype=torch.float64)
+    if n_q % world == 0:                  # equal shards: the bench's exchange step
+        got = {}
+        for root in (None, 0):            # all-gather, and gather-to-root (what bench.py uses)
+            ex = shard.Exchange(hi - lo, "cpu", root=root)
+            ex.start(torch.from_numpy(r), torch.from_numpy(J), local)
+            r_all, J_all, stats = ex.wait()
+            got[root] = torch.cat([r_all[:, None], J_all], 1)
+            assert len(r_all) == (n_q if (root is None or rank == 0) else 0)
+        if rank == 0:
+            assert torch.equal(got[None], got[0])
+        allb = got[None]
+        stats = stats.clone()
+    else:                                 # ragged shards
         allb = shard.gather_ragged(block)
+        stats = shard.reduce_stats(float(local[0]), int(local[1]), int(local[2]))
     idx = shard.gather_ragged(torch.from_numpy(rec["idx"]))
     if rank == 0:
         np.savez(os.path.join(out_dir, "sharded.npz"), block=allb.numpy(), idx=idx.numpy(), stats=stats.numpy())
