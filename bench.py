@@ -52,6 +52,8 @@ def parse_args():
     ap.add_argument("--cloud", type=int, default=0, help="override cloud size")
     ap.add_argument("--queries", type=int, default=0, help="override queries per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather"],
+                    help="N > 1: all-gather the r / J blocks to every rank (default) or gather them to rank 0")
     ap.add_argument("--zbuf-images", type=int, default=6, help="images per GPU of the depth-projection leg (0 = skip)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work of the cpu_baseline sample")
     return ap.parse_args()
@@ -147,7 +149,8 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
                        "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
                        "parallelism": f"queries sharded x{world}, cloud+index replicated",
                        "exchange": "none (1 GPU)" if world == 1 else
-                       "per pass: gather to rank 0 of r and J fp64 blocks (32 B/query) + all_reduce of sum r^2, NCCL on a side stream overlapping the next pass"}}
+                       f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J fp64 blocks (32 B/query) + "
+                       "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass"}}
 
 
 def cpu_pass(orc, tree, q, rng, threads):
@@ -321,7 +324,7 @@ def run_b200(args):
     d_rb = [d_r, torch.empty_like(d_r)] if world > 1 else [d_r]
     d_Jb = [d_J, torch.empty_like(d_J)] if world > 1 else [d_J]
     shard = load_shard()
-    gather = shard.Exchange(Q, dev, root=0) if world > 1 else None
+    gather = shard.Exchange(Q, dev, root=0 if args.exchange == "gather" else None) if world > 1 else None
     step_no = [0]
     flush = None if Q * 24 > 126e6 * 2 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream

@@ -54,7 +54,8 @@ class Exchange:
         self.r_all = torch.empty(full, dtype=torch.float64, device=dev)
         self.J_all = torch.empty((full, 3), dtype=torch.float64, device=dev)
         self.stats = torch.zeros(3, dtype=torch.float64, device=dev)
-        self.stream = torch.cuda.Stream(device=dev) if self.cuda else None
+        # high priority: the collective's CTAs must not queue behind the search kernels' 60 k-block grids
+        self.stream = torch.cuda.Stream(device=dev, priority=-1) if self.cuda else None
         self.events = [torch.cuda.Event() for _ in range(2)] if self.cuda else None
         self.pending = [False, False]
 
