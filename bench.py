@@ -29,6 +29,9 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as entry  # noqa: E402
 
 ALG_BYTES_NN = 260.0       # 12 B query + 8 B result + one 15-point leaf x 16 B
+# dram__bytes_read.sum + dram__bytes_write.sum of k_nn_search + k_nn_far from the one `ncu --set full` capture of the
+# default workload (profiles/r01_ncu_nn_v5_summary.txt: 3.768 + 0.866 + 1.063 + 0.079 GB for 16 M queries)
+NCU_TRAFFIC_NN_SWEEP50M = 5.776e9
 ALG_BYTES_RECORD = 56.0
 ALG_BYTES_RESJAC = 96.0
 WEIGHTS = (10.0, 1000.0, 10000.0)          # proj / icp / icp_ground (src/controllers/incremental_mapper.h:74-78)
@@ -435,7 +438,9 @@ def run_b200(args):
                              "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                              "api": "pcd_associate_evaluate_batch (host pointers, pinned; chunked H2D / kernels / D2H pipeline)"},
                      "roofline": {"bound": "hbm", "kernel": "k_nn_search + k_nn_far (timed together)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                                  "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                                  "frac": achieved / peak,
+                                  "traffic": NCU_TRAFFIC_NN_SWEEP50M if (args.workload == "sweep50m" and Q == 16_000_000 and n_cloud == 50_000_000) else None,
+                                  "traffic_source": "profiles/r01_ncu_nn_v5_summary.txt (bytes per launch pair)", "peak_source": peak_src,
                                   "algorithmic_bytes_per_query": ALG_BYTES_NN, "queries_per_launch": Q,
                                   "avg_launch_ms": 1e3 * nn_avg_s, "launches_timed": int(nn_n)},
                      "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktime.items()},
