@@ -86,6 +86,7 @@ struct Query {
   float px, py, pz;          // q - origin
   int ix, iy, iz;            // own cell (clamped into the grid)
   float R2;                  // conservative float bound on radius^2 (INFINITY when unbounded)
+  float rw;                  // the record's radius word (float radius rounded up, INFINITY, or NaN = invalid)
   unsigned long long best;   // (float bits of d2 << 32) | original index
 
   __device__ __forceinline__ float best_d2() const { return __uint_as_float((unsigned)(best >> 32)); }
@@ -135,8 +136,11 @@ struct Query {
 
   // loads the record of query `i`, derives its cell, radius bound and validity
   __device__ __forceinline__ bool load(const GridView& g, const float4* __restrict__ qrec, uint32_t i) {
-    const float4 r = __ldg(&qrec[i]);
-    qx = r.x; qy = r.y; qz = r.z;
+    return from_record(g, __ldg(&qrec[i]));
+  }
+  __device__ __forceinline__ float4 record() const { return make_float4(qx, qy, qz, rw); }
+  __device__ __forceinline__ bool from_record(const GridView& g, const float4 r) {
+    qx = r.x; qy = r.y; qz = r.z; rw = r.w;
     px = qx - g.ox; py = qy - g.oy; pz = qz - g.oz;
     ix = clampi((int)floorf(px * g.inv_cx), 0, g.dx - 1);
     iy = clampi((int)floorf(py * g.inv_c), 0, g.dy - 1);
@@ -419,7 +423,9 @@ __global__ void k_nn_radius_filter(const double* __restrict__ q, RadiusSrc rs, i
 }
 
 // phase 1: one thread per (cell-sorted) query; uncertified queries go to the far queue
-struct FarItem { unsigned long long best; uint32_t i; uint32_t pad; };
+// queue entry of an uncertified query: its state after phase 1 and its record, so that phase 2 starts from ONE
+// aligned 32-byte load (prefetched one query ahead) instead of the dependent chain far[e] -> qrec[i]
+struct __align__(16) FarItem { unsigned long long best; uint32_t i; uint32_t pad; float4 rec; };
 
 template <int K1>
 __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridView g, const float4* __restrict__ qrec,
@@ -442,7 +448,7 @@ __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridVie
     if (lane == leader) base = atomicAdd(far_count, (unsigned)__popc(m));
     base = __shfl_sync(act, base, leader);
     if (!resolved) {
-      FarItem it; it.best = Q.best; it.i = i; it.pad = 0;
+      FarItem it; it.best = Q.best; it.i = i; it.pad = 0; it.rec = Q.record();
       far[base + __popc(m & ((1u << lane) - 1u))] = it;
     }
   }
@@ -456,14 +462,20 @@ __global__ void __launch_bounds__(NN_THREADS, FAR_MIN_BLOCKS) k_nn_far(GridView 
   const cg::thread_block_tile<FAR_GROUP> tile = cg::tiled_partition<FAR_GROUP>(cg::this_thread_block());
   constexpr unsigned per_block = NN_THREADS / FAR_GROUP;
   const unsigned groups = gridDim.x * per_block;
-  for (unsigned e = blockIdx.x * per_block + threadIdx.x / FAR_GROUP; e < count; e += groups) {
-    const FarItem it = far[e];
+  unsigned e = blockIdx.x * per_block + threadIdx.x / FAR_GROUP;
+  if (e >= count) return;
+  const uint4* fq = reinterpret_cast<const uint4*>(far);
+  uint4 h0 = __ldg(&fq[2 * (size_t)e]), h1 = __ldg(&fq[2 * (size_t)e + 1]);
+  for (; e < count; e += groups) {
+    const uint4 c0 = h0, c1 = h1;
+    if (e + groups < count) { h0 = __ldg(&fq[2 * (size_t)(e + groups)]); h1 = __ldg(&fq[2 * (size_t)(e + groups) + 1]); }   // next query, in flight during this one
+    const uint32_t i = c0.z;
     Query Q;
-    Q.load(g, qrec, it.i);
-    Q.best = it.best;
+    Q.from_record(g, make_float4(__uint_as_float(c1.x), __uint_as_float(c1.y), __uint_as_float(c1.z), __uint_as_float(c1.w)));
+    Q.best = ((unsigned long long)c0.y << 32) | c0.x;
     FarSearch<FAR_GROUP> F(g, Q, tile);
     F.run();
-    if (tile.thread_rank() == 0) nn_write(Q.best, it.i, idx_out, d2_out);
+    if (tile.thread_rank() == 0) nn_write(Q.best, i, idx_out, d2_out);
   }
 }
 
@@ -497,10 +509,16 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
     PCD_LAUNCH_CHECK(ctx);
     if (sorted) {
       int bits = 1; while (((int64_t)1 << bits) < cloud->n_cells && bits < 32) bits++;
+      // The order only has to make neighbouring lanes touch neighbouring cells: the lowest key bits (position
+      // inside a short x stretch) may stay unsorted when that saves a whole 8-bit radix pass.
+      int skip = 0;
+      if (const char* e = getenv("PCD_B200_SORT_SKIP")) skip = atoi(e);
+      else if (bits > 24 && bits <= 28) skip = bits - 24;
+      if (skip < 0 || skip >= bits) skip = 0;
       size_t tmp = 0;
-      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, kb, vb, (int)n, 0, bits, st));
+      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, kb, vb, (int)n, skip, bits, st));
       PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
-      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, kb, vb, (int)n, 0, bits, st));
+      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, kb, vb, (int)n, skip, bits, st));
       order = vb.Current();
     }
   }
