@@ -3,6 +3,7 @@
 // normal_x normal_y normal_z (also accepted: nx ny nz), ASCII or binary little-endian.
 // Missing normal fields read as 0, like PCL leaves unmatched fields at their default.
 #include <stdint.h>
+#include <cmath>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -150,6 +151,100 @@ extern "C" int pcd_ply_write(const char* path, const float* aos8, int64_t n, int
     float row[6] = {p[0], p[1], p[2], p[4], p[5], p[6]};
     if (binary) fwrite(row, sizeof(float), 6, f);
     else fprintf(f, "%.9g %.9g %.9g %.9g %.9g %.9g\n", row[0], row[1], row[2], row[3], row[4], row[5]);
+  }
+  fclose(f);
+  return PCD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// N4  pose prior file "pose.ply" (src/controllers/incremental_mapper.cc:922-997, IncrementalMapperController::LoadPose):
+// ASCII, one line per image after `end_header`: x y z roll pitch yaw in the LIDAR frame (radians).  image_id counts
+// lines from 1; a line containing the token "nan" is skipped but still consumes its id.  Conversion to the camera
+// frame: t_wc = (-y, -z, x); R_wc = AngleAxis(-yaw, Y) * AngleAxis(-pitch, X) * AngleAxis(roll, Z);
+// R_cw = R_wc^T, t_cw = -R_cw t_wc, q_cw = Quaterniond(R_cw).  Output row: image_id, then tx ty tz qw qx qy qz (the
+// order of the reference's trans_pose vector).  Host-side format code: a few hundred rows per reconstruction.
+// ------------------------------------------------------------------------------------------------------------
+static void rot_axis(int axis, double a, double R[9]) {           // Eigen::AngleAxisd(a, UnitX/Y/Z).toRotationMatrix()
+  const double c = cos(a), s = sin(a);
+  const double I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  memcpy(R, I, sizeof I);
+  const int i = (axis + 1) % 3, j = (axis + 2) % 3;
+  R[3 * i + i] = c; R[3 * i + j] = -s; R[3 * j + i] = s; R[3 * j + j] = c;
+}
+static void mat3_mul(const double A[9], const double B[9], double C[9]) {
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 3; c++) C[3 * r + c] = A[3 * r] * B[c] + A[3 * r + 1] * B[3 + c] + A[3 * r + 2] * B[6 + c];
+}
+static void mat3_to_quat(const double m[9], double q[4]) {        // Eigen::Quaternion(Matrix3) (Shoemake), w x y z
+  double t = m[0] + m[4] + m[8];
+  if (t > 0) {
+    t = sqrt(t + 1.0); q[0] = 0.5 * t; t = 0.5 / t;
+    q[1] = (m[7] - m[5]) * t; q[2] = (m[2] - m[6]) * t; q[3] = (m[3] - m[1]) * t;
+  } else {
+    int i = 0;
+    if (m[4] > m[0]) i = 1;
+    if (m[8] > m[4 * i]) i = 2;
+    const int j = (i + 1) % 3, k = (j + 1) % 3;
+    t = sqrt(m[4 * i] - m[4 * j] - m[4 * k] + 1.0);
+    q[1 + i] = 0.5 * t; t = 0.5 / t;
+    q[0] = (m[3 * k + j] - m[3 * j + k]) * t;
+    q[1 + j] = (m[3 * j + i] + m[3 * i + j]) * t;
+    q[1 + k] = (m[3 * k + i] + m[3 * i + k]) * t;
+  }
+}
+
+extern "C" int pcd_pose_ply_read(const char* path, int64_t* image_ids, double* tq7, int64_t capacity, int64_t* n_out) {
+  if (!path || !n_out || (capacity > 0 && (!image_ids || !tq7))) return fail(PCD_E_INVALID, "pcd_pose_ply_read: NULL argument");
+  *n_out = 0;
+  std::ifstream f(path);
+  if (!f) return fail(PCD_E_IO, std::string("failed to open the pose file ") + path);
+  std::string line;
+  bool header_done = false;
+  int64_t image_id = 0, n = 0;
+  while (std::getline(f, line)) {
+    if (!line.empty() && line.back() == '\r') line.pop_back();
+    if (!header_done) { if (line == "end_header") header_done = true; continue; }
+    image_id++;
+    std::istringstream tok(line);
+    std::string s; bool has_nan = false;
+    while (tok >> s) if (s == "nan") { has_nan = true; break; }
+    if (has_nan) continue;
+    std::istringstream ss(line);
+    double v[6]; int k = 0; double d;
+    while (k < 6 && (ss >> d)) v[k++] = d;
+    if (k < 6) return fail(PCD_E_IO, std::string(path) + ": pose line with fewer than 6 numbers");
+    const double twc[3] = {-v[1], -v[2], v[0]};
+    double Rr[9], Rp[9], Ry[9], T[9], Rwc[9];
+    rot_axis(2, v[3], Rr); rot_axis(0, -v[4], Rp); rot_axis(1, -v[5], Ry);
+    mat3_mul(Ry, Rp, T); mat3_mul(T, Rr, Rwc);
+    double Rcw[9];
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) Rcw[3 * r + c] = Rwc[3 * c + r];
+    double q[4]; mat3_to_quat(Rcw, q);
+    if (n < capacity) {
+      image_ids[n] = image_id;
+      double* o = tq7 + 7 * n;
+      for (int r = 0; r < 3; r++) o[r] = -(Rcw[3 * r] * twc[0] + Rcw[3 * r + 1] * twc[1] + Rcw[3 * r + 2] * twc[2]);
+      o[3] = q[0]; o[4] = q[1]; o[5] = q[2]; o[6] = q[3];
+    }
+    n++;
+  }
+  *n_out = n;            // rows available; call again with a larger buffer if n > capacity
+  return PCD_OK;
+}
+
+// Writer of the same file (the reference writes it from GUI code, src/ui/main_window.cc:1096-1160): x y z roll pitch yaw.
+extern "C" int pcd_pose_ply_write(const char* path, const double* xyzrpy, int64_t n) {
+  if (!path || (!xyzrpy && n > 0)) return fail(PCD_E_INVALID, "pcd_pose_ply_write: NULL argument");
+  FILE* f = fopen(path, "w");
+  if (!f) return fail(PCD_E_IO, std::string("cannot open ") + path);
+  fprintf(f, "ply\nformat ascii 1.0\nelement vertex %lld\nproperty float x\nproperty float y\nproperty float z\n"
+             "property float roll\nproperty float pitch\nproperty float yaw\nend_header\n", (long long)n);
+  for (int64_t i = 0; i < n; i++) {
+    const double* p = xyzrpy + 6 * i;
+    bool nan = false;
+    for (int k = 0; k < 6; k++) nan |= std::isnan(p[k]);
+    if (nan) fprintf(f, "nan nan nan nan nan nan\n");
+    else fprintf(f, "%.17g %.17g %.17g %.17g %.17g %.17g\n", p[0], p[1], p[2], p[3], p[4], p[5]);
   }
   fclose(f);
   return PCD_OK;

@@ -373,3 +373,23 @@ def ply_write(path, aos8, binary=True):
     rc = lib().pcd_ply_write(path.encode(), _ptr(a), C.c_int64(len(a)), C.c_int(int(binary)))
     if rc:
         raise PcdError(f"pcd_ply_write failed ({rc}): {lib().pcd_last_error(None).decode()}")
+
+
+def pose_ply_read(path):
+    """pcd_pose_ply_read: returns (image_ids int64 [n], poses float64 [n, 7] = tx ty tz qw qx qy qz)."""
+    n = C.c_int64(0)
+    rc = lib().pcd_pose_ply_read(path.encode(), None, None, C.c_int64(0), C.byref(n))
+    if rc:
+        raise PcdError(lib().pcd_last_error(None).decode())
+    ids = np.empty(n.value, dtype=np.int64); tq = np.empty((n.value, 7), dtype=np.float64)
+    rc = lib().pcd_pose_ply_read(path.encode(), _ptr(ids), _ptr(tq), C.c_int64(n.value), C.byref(n))
+    if rc:
+        raise PcdError(lib().pcd_last_error(None).decode())
+    return ids, tq
+
+
+def pose_ply_write(path, xyzrpy):
+    a = _f64(xyzrpy, 6)
+    rc = lib().pcd_pose_ply_write(path.encode(), _ptr(a), C.c_int64(len(a)))
+    if rc:
+        raise PcdError(lib().pcd_last_error(None).decode())

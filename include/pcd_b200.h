@@ -100,6 +100,13 @@ PCD_API int pcd_ply_read(const char* path, float** aos8, int64_t* n);
 PCD_API int pcd_ply_write(const char* path, const float* aos8, int64_t n, int binary);
 PCD_API void pcd_free(void* p);
 
+/* Pose-prior file "pose.ply" (src/controllers/incremental_mapper.cc:922-997, LoadPose): lidar-frame x y z roll pitch
+ * yaw per image -> rows [tx ty tz qw qx qy qz] of the camera-frame pose, image_ids counting lines from 1 (lines with
+ * "nan" are skipped).  *n = rows available; at most `capacity` rows are stored.  The writer emits the same format
+ * (the reference's writer lives in GUI code, src/ui/main_window.cc:1096-1160). */
+PCD_API int pcd_pose_ply_read(const char* path, int64_t* image_ids, double* tq7, int64_t capacity, int64_t* n);
+PCD_API int pcd_pose_ply_write(const char* path, const double* xyzrpy, int64_t n);
+
 /* Upload a cloud.  direction_trans != 0 applies PointCloudDirectionTrans on the device
  * ((x,y,z)<-(-y,-z,x), same for normals, NaN rows dropped, order kept: src/lidar/ply.cc:33-57).
  * Replaces the data half of PointCloudProcess::Initialize (src/lidar/ply.cc:9-31). */

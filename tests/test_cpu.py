@@ -257,3 +257,28 @@ def test_feature_pixels_truncate(orc):
     px = orc.feature_pixels([[9.99, 4.99], [-0.1, 3.0], [-6.0, 3.0], [4031.9, 3023.9], [4035.0, 10.0]], 0.2, 4032, 3024)
     # (xy * s).cast<int>() truncates toward zero: -0.02 -> 0 is in bounds, -1.2 -> -1 is not
     assert list(px) == [0 * 806 + 1, 0 * 806 + 0, -1, 604 * 806 - 1 - 0, -1] or px[0] == 1
+
+
+# ------------------------------------------------------------------ N4: pose.ply format ---------
+def test_pose_ply_roundtrip_matches_reference_conversion(pcd, tmp_path):
+    """LoadPose (src/controllers/incremental_mapper.cc:922-997) restated with scipy rotations."""
+    from scipy.spatial.transform import Rotation as Rot
+    rng = np.random.default_rng(11)
+    poses = np.concatenate([rng.uniform(-30, 30, (40, 3)), rng.uniform(-np.pi, np.pi, (40, 3))], 1)
+    poses[7] = np.nan                                           # skipped, but its image id is consumed
+    path = str(tmp_path / "pose.ply")
+    pcd.pose_ply_write(path, poses)
+    ids, tq = pcd.pose_ply_read(path)
+    keep = [i for i in range(40) if i != 7]
+    assert np.array_equal(ids, np.asarray(keep) + 1)
+    for row, i in zip(tq, keep):
+        x, y, z, roll, pitch, yaw = poses[i]
+        R_wc = (Rot.from_rotvec([0, -yaw, 0]) * Rot.from_rotvec([-pitch, 0, 0]) * Rot.from_rotvec([0, 0, roll])).as_matrix()
+        R_cw = R_wc.T
+        t_cw = -R_cw @ np.array([-y, -z, x])
+        assert np.allclose(row[0:3], t_cw, rtol=1e-12, atol=1e-12)
+        q = row[3:7]                                            # w x y z
+        R_back = Rot.from_quat([q[1], q[2], q[3], q[0]]).as_matrix()
+        assert np.allclose(R_back, R_cw, atol=1e-12) and abs(np.linalg.norm(q) - 1) < 1e-12
+    with pytest.raises(pcd.PcdError):
+        pcd.pose_ply_read(str(tmp_path / "missing.ply"))
