@@ -58,6 +58,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather"],
                     help="N > 1: all-gather the r / J blocks to every rank (default) or gather them to rank 0")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (query-count sweeps only; the default line carries it)")
+    ap.add_argument("--zbuf-scale", type=float, default=1.0, help="depth_image_scale of the depth-projection leg (reference default 0.2)")
     ap.add_argument("--zbuf-images", type=int, default=6, help="images per GPU of the depth-projection leg (0 = skip)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work of the cpu_baseline sample")
     return ap.parse_args()
@@ -198,11 +200,11 @@ def cpu_baseline(orc, world_cloud, q, opt_num, seconds):
             "assoc_queries_per_s": m / ta, "resjac_evals_per_s": m / tr, "accepted_frac": float(rec["accepted"].mean())}, tree
 
 
-def zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, n_img, rank, world):
+def zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, n_img, rank, world, scale=1.0):
     """Secondary metric (SURVEY.md 8d, configs[3]): depth projection of the resident cloud into this rank's images at
     1920x1080, depth_image_scale 1.0, 3000 keypoints each -- PcdProj::SetNewImage through the host-pointer C ABI
     (feature z-buffer, winners copied back), plus one dense z-buffer (the if_save_depth_image map)."""
-    opt = pcd.ProjOptions.default(depth_image_scale=1.0)
+    opt = pcd.ProjOptions.default(depth_image_scale=scale)
     t0 = time.perf_counter()
     cloud.build_submap(opt)
     t_sub = time.perf_counter() - t0
@@ -223,7 +225,7 @@ def zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, n_img, rank, world):
     t0 = time.perf_counter()
     _, _, z, dstats = cloud.project_image(imgs[0], coef, None, dense=True)
     dt_dense = time.perf_counter() - t0
-    return {"images": len(imgs), "image_size": [1920, 1080], "depth_image_scale": 1.0, "features_per_image": len(feats),
+    return {"images": len(imgs), "image_size": [1920, 1080], "depth_image_scale": scale, "features_per_image": len(feats),
             "submap_build_s": t_sub, "images_per_s": len(imgs) / dt, "point_projections_per_s": float(stats[1]) / dt,
             "pixel_updates_per_s": float(stats[2]) / dt, "points_projected": int(stats[1]), "pixel_updates": int(stats[2]),
             "features_hit": int(stats[3]), "k_project_ms_per_image": k_ms / max(k_n, 1),
@@ -403,37 +405,38 @@ def run_b200(args):
     gpu_ms_max = float(mx[0].item())
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- end to end: the host-pointer C ABI, pinned host buffers, H2D + D2H inside the timed region ----
-    fields = ("idx", "accepted", "type", "xyz", "abcd", "dist")
-    shapes = {"idx": ((Q,), np.int32), "accepted": ((Q,), np.uint8), "type": ((Q,), np.uint8), "xyz": ((Q, 3), np.float64),
-              "abcd": ((Q, 4), np.float64), "dist": ((Q,), np.float64)}
-    h_out = {f: pcd.pinned_empty(*shapes[f]) for f in fields}
-    h_w = pcd.pinned_empty((Q,), np.float64)
-    h_r = pcd.pinned_empty((Q,), np.float64)
-    h_J = pcd.pinned_empty((Q, 3), np.float64)
+    e2e_steps, e2e_s, h2d, d2h = 0, 1.0, 0, 0
+    if not args.no_e2e:
+        # ---- end to end: the host-pointer C ABI, pinned host buffers, H2D + D2H inside the timed region ----
+        fields = ("idx", "accepted", "type", "xyz", "abcd", "dist")
+        shapes = {"idx": ((Q,), np.int32), "accepted": ((Q,), np.uint8), "type": ((Q,), np.uint8), "xyz": ((Q, 3), np.float64),
+                  "abcd": ((Q, 4), np.float64), "dist": ((Q,), np.float64)}
+        h_out = {f: pcd.pinned_empty(*shapes[f]) for f in fields}
+        h_w = pcd.pinned_empty((Q,), np.float64)
+        h_r = pcd.pinned_empty((Q,), np.float64)
+        h_J = pcd.pinned_empty((Q, 3), np.float64)
 
-    def e2e_step():
-        # the user-facing call: SfM points in host memory -> records + residuals + Jacobian blocks in host memory
-        return cloud.associate_evaluate(h_q, WEIGHTS, opt_num=h_on, sweep=SWEEP, variant=pcd.ASSOC_GLOBAL, fields=fields,
-                                        out=h_out, out_rj=(h_r, h_J))[3]
+        def e2e_step():
+            # the user-facing call: SfM points in host memory -> records + residuals + Jacobian blocks in host memory
+            return cloud.associate_evaluate(h_q, WEIGHTS, opt_num=h_on, sweep=SWEEP, variant=pcd.ASSOC_GLOBAL, fields=fields,
+                                            out=h_out, out_rj=(h_r, h_J))[3]
 
-    e2e_steps = max(2, min(args.steps, 5))
-    e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+        e2e_steps = max(2, min(args.steps, 5))
         e2e_step()
-    barrier()
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_s = float(e2e_s.item())
-    h2d = Q * (24 + 4)
-    d2h = sum(int(np.prod(shapes[f][0])) * np.dtype(shapes[f][1]).itemsize for f in fields) + Q * (8 + 24) + 8 * ((Q + (1 << 20) - 1) >> 20)
-
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        barrier()
+        e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+        e2e_s = float(e2e_s.item())
+        h2d = Q * (24 + 4)
+        d2h = sum(int(np.prod(shapes[f][0])) * np.dtype(shapes[f][1]).itemsize for f in fields) + Q * (8 + 24) + 8 * ((Q + (1 << 20) - 1) >> 20)
     zb = None
     if args.zbuf_images > 0:
-        zb = zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, args.zbuf_images, rank, world)
+        zb = zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, args.zbuf_images, rank, world, args.zbuf_scale)
         if world > 1:
             t = torch.tensor([zb["images_per_s"], zb["point_projections_per_s"], zb["pixel_updates_per_s"]], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
@@ -448,7 +451,7 @@ def run_b200(args):
         line["config"]["passes_per_step"] = passes
         line.update({"value": passes * Q * world / (ms_step * 1e-3), "ms_per_step": ms_step, "gpu_launches": int(launches),
                      "clocks": clocks,
-                     "e2e": {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
+                     "e2e": None if args.no_e2e else {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
                              "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                              "api": "pcd_associate_evaluate_batch (host pointers, pinned; chunked H2D / kernels / D2H pipeline)"},
                      "roofline": {"bound": "hbm", "kernel": "k_nn_search + k_nn_far (timed together)", "achieved": achieved, "peak": peak, "unit": "GB/s",
