@@ -123,6 +123,18 @@ int main(int argc, char** argv) {
     pcp.pcd_proj_->SetNewImage(image, cam, m);
     out.push_back((double)m.size());
     for (auto& kv : m) { out.push_back((double)kv.first); for (int c = 0; c < 6; c++) out.push_back(kv.second(c)); }
+    // the batched Project2Image form must fill the cache with exactly the same maps
+    MockImage image2 = image; image2.t(0) += 1.0;
+    std::map<uint64_t, std::map<uint64_t, Eigen::Vector6d>> cache;
+    pcp.pcd_proj_->SetNewImages<MockImage, MockCamera>({&image, &image2}, {&cam, &cam}, {7, 9}, cache);
+    std::map<uint64_t, Eigen::Vector6d> m2;
+    pcp.pcd_proj_->SetNewImage(image2, cam, m2);
+    auto same = [](const std::map<uint64_t, Eigen::Vector6d>& a, const std::map<uint64_t, Eigen::Vector6d>& b) {
+      if (a.size() != b.size()) return false;
+      for (auto& kv : a) { auto it = b.find(kv.first); if (it == b.end()) return false; for (int c = 0; c < 6; c++) if (it->second(c) != kv.second(c)) return false; }
+      return true;
+    };
+    if (cache.size() != 2 || !same(cache[7], m) || !same(cache[9], m2)) { fprintf(stderr, "batched SetNewImages differs from SetNewImage\n"); return 1; }
   }
   FILE* f = fopen(argv[3], "wb");
   if (!f || fwrite(out.data(), 8, out.size(), f) != out.size()) return 1;

@@ -242,6 +242,45 @@ class PcdProj {                      // src/lidar/pcd_projection.h:49-66
       map.insert({(typename MapT::key_type)ids[k], v});       // map.insert keeps the first, as :75
     }
   }
+  // Batched form of the loop in BundleAdjustmentConfig::Project2Image (src/optim/bundle_adjustment.cc:241-281): the
+  // caller collects the images that are not cached yet (its own decision logic, :247-258, is unchanged) and projects
+  // them in ONE call (pcd_project_images); cache[image_id] receives what SetNewImage(image, camera, map) would fill.
+  template <typename ImageT, typename CameraT, typename CacheT>
+  void SetNewImages(const std::vector<const ImageT*>& images, const std::vector<const CameraT*>& cameras,
+                    const std::vector<uint64_t>& image_ids, CacheT& cache) {
+    if (!ready_ || images.empty()) return;
+    std::vector<pcd_image> ims; std::vector<double> feat; std::vector<uint64_t> ids; std::vector<int64_t> start(1, 0);
+    for (size_t k = 0; k < images.size(); k++) {
+      ims.push_back(MakeImage(*images[k], *cameras[k]));
+      for (const auto& p2 : images[k]->Points2D()) {
+        if (!p2.HasPoint3D()) continue;
+        const auto xy = p2.XY();
+        feat.push_back(xy(0)); feat.push_back(xy(1)); ids.push_back((uint64_t)p2.GetPoint3DId());
+      }
+      start.push_back((int64_t)ids.size());
+    }
+    std::vector<int32_t> win(ids.size()); std::vector<float> rng(ids.size());
+    DropinRuntime& rt = DropinRuntime::Get();
+    {
+      std::lock_guard<std::mutex> g(rt.mu);
+      pcd_proj_options o = options_.ToC();
+      double* coef = SplatCoef(ims[0], o);
+      if (pcd_project_images(dev_->h, ims.data(), (int64_t)ims.size(), coef, feat.data(), start.data(), win.data(), rng.data(), nullptr) != PCD_OK) {
+        rt.error = pcd_last_error(rt.ctx); return;
+      }
+    }
+    for (size_t k = 0; k < images.size(); k++) {
+      auto& map = cache[(typename CacheT::key_type)image_ids[k]];
+      for (int64_t f = start[k]; f < start[k + 1]; f++) {
+        if (win[f] < 0) continue;
+        const LidarPoint& l = global_map_ptr_->points[(size_t)win[f]];
+        typename CacheT::mapped_type::mapped_type v;
+        v(0) = l.x; v(1) = l.y; v(2) = l.z; v(3) = l.normal_x; v(4) = l.normal_y; v(5) = l.normal_z;
+        map.insert({(typename CacheT::mapped_type::key_type)ids[f], v});
+      }
+    }
+  }
+
   // pcd_projection.cc:102-220 (initial image pair): pt_xys[k].second = matched, pt_xyzs[k] = camera-frame point.
   template <typename ImageT, typename CameraT, typename XYs, typename XYZs>
   void SetNewImage(const ImageT& image, const CameraT& camera, XYs& pt_xys, XYZs& pt_xyzs) {
@@ -280,6 +319,12 @@ class PcdProj {                      // src/lidar/pcd_projection.h:49-66
     im.width = (int32_t)camera.Width(); im.height = (int32_t)camera.Height();
     return im;
   }
+  // the function-local statics a_x b_x a_y b_y of pcd_projection.cc:391-397: fixed by the first camera of the process
+  static double* SplatCoef(const pcd_image& im, const pcd_proj_options& o) {
+    static double coef[4]; static bool have_coef = false;
+    if (!have_coef) { pcd_splat_coef(im.cam, &o, coef); have_coef = true; }
+    return coef;
+  }
   template <typename ImageT, typename CameraT>
   bool Project(const ImageT& image, const CameraT& camera, const std::vector<double>& feat, std::vector<int32_t>& win,
                std::vector<float>& rng) {
@@ -287,9 +332,7 @@ class PcdProj {                      // src/lidar/pcd_projection.h:49-66
     DropinRuntime& rt = DropinRuntime::Get();
     std::lock_guard<std::mutex> g(rt.mu);
     pcd_proj_options o = options_.ToC();
-    // the function-local statics of pcd_projection.cc:391-397: fixed by the first camera of the process
-    static double coef[4]; static bool have_coef = false;
-    if (!have_coef) { pcd_splat_coef(im.cam, &o, coef); have_coef = true; }
+    double* coef = SplatCoef(im, o);
     if (pcd_project_image(dev_->h, &im, coef, feat.data(), (int64_t)win.size(), win.data(), rng.data(), nullptr, nullptr) != PCD_OK) {
       rt.error = pcd_last_error(rt.ctx); return false;
     }
