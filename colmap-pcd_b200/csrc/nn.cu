@@ -248,14 +248,6 @@ struct FarSearch {
     return v;
   }
 
-  // squared lower bound to cubic cell `bit` of block (X, Y, Z)
-  __device__ __forceinline__ float cell_lb2(int X, int Y, int Z, int bit) const {
-    const int cxc = 4 * X + (bit & 3), cy = 4 * Y + ((bit >> 2) & 3), cz = 4 * Z + (bit >> 4);
-    float a = Query::gap(Q.px, cxc * g.xs, cxc * g.xs + g.xs - 1, g.cx, g.margin),
-          b = Query::gap(Q.py, cy, cy, g.c, g.margin), c = Query::gap(Q.pz, cz, cz, g.c, g.margin);
-    return (a * a + (b * b + c * c)) * SHRINK;
-  }
-
   // squared lower bound to the whole block (X, Y, Z)
   __device__ __forceinline__ float block_lb2(int X, int Y, int Z) const {
     const int sx = 4 * g.xs;
@@ -283,13 +275,20 @@ struct FarSearch {
   // whole group, uniform arguments: the occupied cells of one block in order of increasing box distance
   // (64 / G cells per lane), stopping at the first cell that can no longer beat the group's bound
   __device__ __forceinline__ void scan_block(int X, int Y, int Z, unsigned long long w) {
+    static_assert(G == 16 || G == 32, "cell bit = lane + G * h must keep x and y fixed per lane");
     constexpr int H = 64 / G;
     unsigned key[H];
+    // cell `bit` = (z << 4) | (y << 2) | x of the block: a lane's cells share x = lane & 3 and y = (lane >> 2) & 3,
+    // so the x and y gaps are computed once per lane and only the z gap changes with h
+    const int cxc = 4 * X + (lane & 3), cy = 4 * Y + ((lane >> 2) & 3);
+    const float ga = Query::gap(Q.px, cxc * g.xs, cxc * g.xs + g.xs - 1, g.cx, g.margin), gb = Query::gap(Q.py, cy, cy, g.c, g.margin);
+    const float gab2 = ga * ga + gb * gb;
 #pragma unroll
     for (int h = 0; h < H; h++) {
-      const int bit = lane + G * h;
+      const int bit = lane + G * h, cz = 4 * Z + (bit >> 4);
+      const float gc = Query::gap(Q.pz, cz, cz, g.c, g.margin);
       // lb >= 0, so its bit pattern orders like the value; the low 6 bits carry the cell (lb rounded DOWN: conservative)
-      key[h] = ((w >> bit) & 1ull) ? ((__float_as_uint(cell_lb2(X, Y, Z, bit)) & ~63u) | (unsigned)bit) : 0xffffffffu;
+      key[h] = ((w >> bit) & 1ull) ? ((__float_as_uint((gab2 + gc * gc) * SHRINK) & ~63u) | (unsigned)bit) : 0xffffffffu;
     }
     for (;;) {
       unsigned k = key[0];
@@ -424,7 +423,7 @@ __global__ void k_nn_radius_filter(const double* __restrict__ q, RadiusSrc rs, i
 
 // phase 1: one thread per (cell-sorted) query; uncertified queries go to the far queue
 // queue entry of an uncertified query: its state after phase 1 and its record, so that phase 2 starts from ONE
-// aligned 32-byte load (prefetched one query ahead) instead of the dependent chain far[e] -> qrec[i]
+// aligned 32-byte load instead of the dependent chain far[e] -> qrec[i]
 struct __align__(16) FarItem { unsigned long long best; uint32_t i; uint32_t pad; float4 rec; };
 
 template <int K1>
@@ -454,21 +453,21 @@ __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridVie
   }
 }
 
-// phase 2: one group of FAR_GROUP lanes per far query, grid-stride over the queue
-__global__ void __launch_bounds__(NN_THREADS, FAR_MIN_BLOCKS) k_nn_far(GridView g, const float4* __restrict__ qrec,
-                                                       int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
-                                                       const FarItem* __restrict__ far, const unsigned int* __restrict__ far_count) {
+// phase 2: one group of FAR_GROUP lanes per far query.  Persistent blocks (exactly one resident wave); the groups
+// draw queue entries from an atomic counter, because the cost of a far query varies by an order of magnitude
+// (a query with nothing inside its range walks every block of the ball) and a static split leaves a long tail.
+__global__ void __launch_bounds__(NN_THREADS, FAR_MIN_BLOCKS) k_nn_far(GridView g, int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
+                                                       const FarItem* __restrict__ far, const unsigned int* __restrict__ far_count,
+                                                       unsigned int* __restrict__ next) {
   const unsigned count = *far_count;
   const cg::thread_block_tile<FAR_GROUP> tile = cg::tiled_partition<FAR_GROUP>(cg::this_thread_block());
-  constexpr unsigned per_block = NN_THREADS / FAR_GROUP;
-  const unsigned groups = gridDim.x * per_block;
-  unsigned e = blockIdx.x * per_block + threadIdx.x / FAR_GROUP;
-  if (e >= count) return;
   const uint4* fq = reinterpret_cast<const uint4*>(far);
-  uint4 h0 = __ldg(&fq[2 * (size_t)e]), h1 = __ldg(&fq[2 * (size_t)e + 1]);
-  for (; e < count; e += groups) {
-    const uint4 c0 = h0, c1 = h1;
-    if (e + groups < count) { h0 = __ldg(&fq[2 * (size_t)(e + groups)]); h1 = __ldg(&fq[2 * (size_t)(e + groups) + 1]); }   // next query, in flight during this one
+  for (;;) {
+    unsigned e = 0;
+    if (tile.thread_rank() == 0) e = atomicAdd(next, 1u);
+    e = tile.shfl(e, 0);
+    if (e >= count) return;
+    const uint4 c0 = __ldg(&fq[2 * (size_t)e]), c1 = __ldg(&fq[2 * (size_t)e + 1]);
     const uint32_t i = c0.z;
     Query Q;
     Q.from_record(g, make_float4(__uint_as_float(c1.x), __uint_as_float(c1.y), __uint_as_float(c1.z), __uint_as_float(c1.w)));
@@ -528,14 +527,19 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   const int blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
   {
     ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
-    PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 4, st));
+    PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 8, st));    // queue length and the work counter of phase 2
     if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
     else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
     PCD_LAUNCH_CHECK(ctx);
-    int far_blocks = ctx->sm_count * 8;                      // one lane group per queued query, grid-stride
+    static int far_occ = 0;                                  // resident blocks per SM of k_nn_far
+    if (far_occ == 0) {
+      PCD_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&far_occ, k_nn_far, NN_THREADS, 0));
+      if (far_occ < 1) far_occ = 1;
+    }
+    int far_blocks = ctx->sm_count * far_occ;                // one resident wave; groups pull work dynamically
     if ((int64_t)far_blocks * (NN_THREADS / FAR_GROUP) > n) far_blocks = (int)((n + NN_THREADS / FAR_GROUP - 1) / (NN_THREADS / FAR_GROUP));
     ProfScope psf(ctx, PCD_K_NN_FAR, st);
-    k_nn_far<<<far_blocks, NN_THREADS, 0, st>>>(g, qrec, d_idx, d2, far, far_count);
+    k_nn_far<<<far_blocks, NN_THREADS, 0, st>>>(g, d_idx, d2, far, far_count, far_count + 1);
     PCD_LAUNCH_CHECK(ctx);
   }
   if (exact_radius && (d_radius || d_opt_num || fixed_radius != INFINITY)) {
