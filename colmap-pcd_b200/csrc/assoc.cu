@@ -40,11 +40,19 @@ __device__ __forceinline__ void normalize_plane(const double l[6], double abcd[4
   abcd[0] = a; abcd[1] = b; abcd[2] = c; abcd[3] = d;
 }
 
-__global__ void k_assoc_record(const float4* __restrict__ aos, const double* __restrict__ p, const int32_t* __restrict__ nn_idx,
+// Optional fused a18 + a19 (FUSED_EVAL): weight by type (src/optim/bundle_adjustment.cc:1013-1028) and the Jet<double,3>
+// evaluation of the cost function (src/base/cost_functions.h:226-229) at the SfM point itself for ACCEPTED matches, in
+// the operation order of k_resjac (resjac.cu); a rejected query has no residual block in the reference and reports
+// r = 0, J = 0.  The point, plane and type are already in registers here, so the fused pass saves re-reading them.
+struct EvalDev { double wp, wi, wg; double* r; double* J; double* partial; };
+
+template <bool FUSED_EVAL>
+__global__ void __launch_bounds__(256) k_assoc_record(const float4* __restrict__ aos, const double* __restrict__ p, const int32_t* __restrict__ nn_idx,
                                const double* __restrict__ range, const int32_t* __restrict__ opt_num, pcd_range_sweep sw,
-                               int64_t n, int variant, pcd_assoc_out o, unsigned long long* __restrict__ counters) {
+                               int64_t n, int variant, pcd_assoc_out o, unsigned long long* __restrict__ counters, EvalDev ev) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   bool acc = false, ground = false;
+  double rr = 0.0;
   if (i < n) {
     double px = p[3 * i], py = p[3 * i + 1], pz = p[3 * i + 2];
     int32_t idx = nn_idx[i];
@@ -95,6 +103,38 @@ __global__ void k_assoc_record(const float4* __restrict__ aos, const double* __r
     if (o.abcd) { o.abcd[4 * i] = abcd[0]; o.abcd[4 * i + 1] = abcd[1]; o.abcd[4 * i + 2] = abcd[2]; o.abcd[4 * i + 3] = abcd[3]; }
     if (o.dist) o.dist[i] = dist;
     if (o.angle) o.angle[i] = angle;
+    if (FUSED_EVAL) {
+      double J[3] = {0.0, 0.0, 0.0};
+      if (acc) {
+        const double w = type == PCD_TYPE_PROJ ? ev.wp : (type == PCD_TYPE_ICP ? ev.wi : (type == PCD_TYPE_ICP_GROUND ? ev.wg : 0.0));
+        double s = ((px * abcd[0] + py * abcd[1]) + pz * abcd[2]) + abcd[3];
+        double u = 0.0 - s;
+        double f = u * u;
+        double sq = sqrt(f);
+        double inv = 1.0 / (2.0 * sq);
+        rr = w * sq;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          double du = 0.0 - abcd[k];
+          double fv = u * du + du * u;
+          J[k] = w * (fv * inv) + 0.0 * sq;
+        }
+      }
+      ev.r[i] = rr;
+      if (ev.J) { ev.J[3 * i] = J[0]; ev.J[3 * i + 1] = J[1]; ev.J[3 * i + 2] = J[2]; }
+    }
+  }
+  if (FUSED_EVAL && ev.partial) {      // deterministic: fixed tree inside the block, fixed order across blocks
+    double s2 = rr * rr;
+    for (int o2 = 16; o2 > 0; o2 >>= 1) s2 += __shfl_down_sync(0xffffffffu, s2, o2);
+    __shared__ double sh[8];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int k = 0; k < 8; k++) t += sh[k];
+      ev.partial[blockIdx.x] = t;
+    }
   }
   if (counters) {
     unsigned ma = __ballot_sync(0xffffffffu, acc), mg = __ballot_sync(0xffffffffu, acc && ground);
@@ -148,53 +188,6 @@ __global__ void k_match_proj(const double* __restrict__ p, const double* __restr
   if (angle_out) angle_out[i] = ang;
 }
 
-// Fused a18 + a19 for the end-to-end pass: weight by type (src/optim/bundle_adjustment.cc:1013-1028) and the
-// Jet<double,3> evaluation of the cost function (src/base/cost_functions.h:226-229) at the SfM point itself,
-// for ACCEPTED matches; a rejected query has no residual block in the reference and reports r = 0, J = 0.
-// Same operation order as k_resjac (resjac.cu).  partial: per-block sum of r^2 (fixed tree).
-__global__ void __launch_bounds__(256) k_assoc_eval(const double* __restrict__ p, const double* __restrict__ abcd,
-                                                    const uint8_t* __restrict__ accepted, const uint8_t* __restrict__ type,
-                                                    int64_t n, double wp, double wi, double wg, double* __restrict__ r_out,
-                                                    double* __restrict__ J_out, double* __restrict__ partial) {
-  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  double rr = 0.0;
-  if (i < n) {
-    double J[3] = {0.0, 0.0, 0.0};
-    if (accepted[i]) {
-      const uint8_t t = type[i];
-      const double w = t == PCD_TYPE_PROJ ? wp : (t == PCD_TYPE_ICP ? wi : (t == PCD_TYPE_ICP_GROUND ? wg : 0.0));
-      const double a = abcd[4 * i], b = abcd[4 * i + 1], c = abcd[4 * i + 2], d = abcd[4 * i + 3];
-      double s = ((p[3 * i] * a + p[3 * i + 1] * b) + p[3 * i + 2] * c) + d;
-      double u = 0.0 - s;
-      double f = u * u;
-      double sq = sqrt(f);
-      double inv = 1.0 / (2.0 * sq);
-      rr = w * sq;
-      const double nn[3] = {a, b, c};
-#pragma unroll
-      for (int k = 0; k < 3; k++) {
-        double du = 0.0 - nn[k];
-        double fv = u * du + du * u;
-        J[k] = w * (fv * inv) + 0.0 * sq;
-      }
-    }
-    r_out[i] = rr;
-    if (J_out) { J_out[3 * i] = J[0]; J_out[3 * i + 1] = J[1]; J_out[3 * i + 2] = J[2]; }
-  }
-  if (partial) {
-    double s2 = rr * rr;
-    for (int o = 16; o > 0; o >>= 1) s2 += __shfl_down_sync(0xffffffffu, s2, o);
-    __shared__ double sh[8];
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s2;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      double t = 0.0;
-      for (int k = 0; k < 8; k++) t += sh[k];
-      partial[blockIdx.x] = t;
-    }
-  }
-}
-
 __global__ void k_sum_blocks(const double* __restrict__ partial, int nb, double* __restrict__ out) {
   __shared__ double sh[256];
   double s = 0.0;
@@ -214,14 +207,10 @@ struct EvalArgs { double wp, wi, wg; double* r; double* J; double* sum_sq; };
 
 extern "C" {
 
-int pcd_associate_batch_dev(pcd_cloud* cloud, const double* d_p, const double* d_range, const int32_t* d_opt_num,
-                            const pcd_range_sweep* sweep, int64_t n, int variant, const pcd_assoc_out* d_out, void* stream) {
-  if (!cloud) return PCD_E_INVALID;
+static int associate_dev_impl(pcd_cloud* cloud, const double* d_p, const double* d_range, const int32_t* d_opt_num,
+                              const pcd_range_sweep* sweep, int64_t n, int variant, const pcd_assoc_out* d_out,
+                              const pcd::EvalDev* ev, double* d_sum_sq, cudaStream_t st) {
   pcd_ctx* ctx = cloud->ctx;
-  if (n < 0 || !d_out || (n > 0 && !d_p) || variant < 0 || variant > 2) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_associate_batch_dev: bad argument");
-  if (n == 0) return PCD_OK;
-  DeviceGuard g(ctx->device);
-  cudaStream_t st = (cudaStream_t)stream;
   int32_t* d_idx = d_out->idx;
   if (!d_idx) { PCD_CUDA(ctx, ctx->partial.ensure(4 * (size_t)n)); d_idx = ctx->partial.as<int32_t>(); }
   // search radius: the accept test bounds how far a useful neighbour can be
@@ -232,10 +221,43 @@ int pcd_associate_batch_dev(pcd_cloud* cloud, const double* d_p, const double* d
   if (rc) return rc;
   pcd_range_sweep sw = sweep ? *sweep : pcd_range_sweep{0, 0, 0};
   pcd_assoc_out o = *d_out; o.idx = nullptr;   // idx already written by the search (or private)
+  const int nb = pcd_blocks(n, 256);
   pcd::ProfScope ps(ctx, PCD_K_ASSOC_RECORD, st);
-  pcd::k_assoc_record<<<pcd_blocks(n, 256), 256, 0, st>>>((const float4*)cloud->aos, d_p, d_idx, rr, on, sw, n, variant, o, nullptr);
-  PCD_LAUNCH_CHECK(ctx);
+  if (ev) {
+    pcd::EvalDev e = *ev;
+    if (d_sum_sq) { PCD_CUDA(ctx, ctx->eval_partial.ensure(8 * (size_t)nb)); e.partial = ctx->eval_partial.as<double>(); }
+    pcd::k_assoc_record<true><<<nb, 256, 0, st>>>((const float4*)cloud->aos, d_p, d_idx, rr, on, sw, n, variant, o, nullptr, e);
+    PCD_LAUNCH_CHECK(ctx);
+    if (d_sum_sq) { pcd::k_sum_blocks<<<1, 256, 0, st>>>(e.partial, nb, d_sum_sq); PCD_LAUNCH_CHECK(ctx); }
+  } else {
+    pcd::k_assoc_record<false><<<nb, 256, 0, st>>>((const float4*)cloud->aos, d_p, d_idx, rr, on, sw, n, variant, o, nullptr, pcd::EvalDev{});
+    PCD_LAUNCH_CHECK(ctx);
+  }
   return PCD_OK;
+}
+
+int pcd_associate_batch_dev(pcd_cloud* cloud, const double* d_p, const double* d_range, const int32_t* d_opt_num,
+                            const pcd_range_sweep* sweep, int64_t n, int variant, const pcd_assoc_out* d_out, void* stream) {
+  if (!cloud) return PCD_E_INVALID;
+  pcd_ctx* ctx = cloud->ctx;
+  if (n < 0 || !d_out || (n > 0 && !d_p) || variant < 0 || variant > 2) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_associate_batch_dev: bad argument");
+  if (n == 0) return PCD_OK;
+  DeviceGuard g(ctx->device);
+  return associate_dev_impl(cloud, d_p, d_range, d_opt_num, sweep, n, variant, d_out, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+int pcd_associate_evaluate_batch_dev(pcd_cloud* cloud, const double* d_p, const double* d_range, const int32_t* d_opt_num,
+                                     const pcd_range_sweep* sweep, int64_t n, int variant, double w_proj, double w_icp,
+                                     double w_ground, const pcd_assoc_out* d_out, double* d_r, double* d_J, double* d_sum_sq,
+                                     void* stream) {
+  if (!cloud) return PCD_E_INVALID;
+  pcd_ctx* ctx = cloud->ctx;
+  if (n < 0 || !d_out || (n > 0 && (!d_p || !d_r)) || variant < 0 || variant > 2)
+    PCD_FAIL(ctx, PCD_E_INVALID, "pcd_associate_evaluate_batch_dev: bad argument");
+  DeviceGuard g(ctx->device);
+  if (n == 0) { if (d_sum_sq) PCD_CUDA(ctx, cudaMemsetAsync(d_sum_sq, 0, 8, (cudaStream_t)stream)); return PCD_OK; }
+  pcd::EvalDev ev = {w_proj, w_icp, w_ground, d_r, d_J, nullptr};
+  return associate_dev_impl(cloud, d_p, d_range, d_opt_num, sweep, n, variant, d_out, &ev, d_sum_sq, (cudaStream_t)stream);
 }
 
 static int associate_pipeline(pcd_cloud* cloud, const double* p, const double* range, const int32_t* opt_num,
@@ -254,7 +276,7 @@ static int associate_pipeline(pcd_cloud* cloud, const double* p, const double* r
   int64_t nchunks = (n + CH - 1) / CH;
   double* d_chunk_sums = nullptr;
   if (ev && ev->sum_sq) {
-    PCD_CUDA(ctx, ctx->stage_aux[0].ensure(8 * (size_t)nchunks + 8 * (size_t)pcd_blocks(CH, 256) * 2));
+    PCD_CUDA(ctx, ctx->stage_aux[0].ensure(8 * (size_t)nchunks));
     d_chunk_sums = ctx->stage_aux[0].as<double>();
   }
   for (int64_t c = 0; c < nchunks; c++) {
@@ -286,16 +308,14 @@ static int associate_pipeline(pcd_cloud* cloud, const double* p, const double* r
     d.accepted = (out->accepted || ev) ? (uint8_t*)take((size_t)m) : nullptr;
     d.type = (out->type || ev) ? (uint8_t*)take((size_t)m) : nullptr;
     if (c >= 2) PCD_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev[4 + b], 0));             // D2H of chunk c-2 finished
-    int rc = pcd_associate_batch_dev(cloud, d_p, d_range, d_on, sweep, m, variant, &d, st);
-    if (rc) return rc;
+    int rc;
     if (ev) {
-      const int nb = pcd_blocks(m, 256);
-      double* part = d_chunk_sums ? d_chunk_sums + nchunks + (size_t)b * pcd_blocks(CH, 256) : nullptr;
-      pcd::ProfScope ps(ctx, PCD_K_RESJAC, st);
-      pcd::k_assoc_eval<<<nb, 256, 0, st>>>(d_p, d.abcd, d.accepted, d.type, m, ev->wp, ev->wi, ev->wg, d_r, d_J, part);
-      PCD_LAUNCH_CHECK(ctx);
-      if (part) { pcd::k_sum_blocks<<<1, 256, 0, st>>>(part, nb, d_chunk_sums + c); PCD_LAUNCH_CHECK(ctx); }
+      pcd::EvalDev e = {ev->wp, ev->wi, ev->wg, d_r, d_J, nullptr};
+      rc = associate_dev_impl(cloud, d_p, d_range, d_on, sweep, m, variant, &d, &e, d_chunk_sums ? d_chunk_sums + c : nullptr, st);
+    } else {
+      rc = associate_dev_impl(cloud, d_p, d_range, d_on, sweep, m, variant, &d, nullptr, nullptr, st);
     }
+    if (rc) return rc;
     PCD_CUDA(ctx, cudaEventRecord(ctx->ev[2 + b], st));
     PCD_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ctx->ev[2 + b], 0));
     cudaStream_t co = ctx->copy_out;

@@ -293,6 +293,17 @@ class Cloud:
                        "pcd_associate_evaluate_batch")
         return res, rr, J, s.value
 
+    def associate_evaluate_dev(self, d_p, d_range, d_opt_num, sweep, n, variant, weights, out_ptrs, d_r, d_J, d_sum, stream=0):
+        """pcd_associate_evaluate_batch_dev: device pointers (ints); out_ptrs: dict field -> device pointer."""
+        allf = ("idx", "accepted", "type", "rgb", "xyz", "abcd", "dist", "angle")
+        out = AssocOut(*[out_ptrs.get(f) for f in allf])
+        sw = None if sweep is None else RangeSweep(*sweep)
+        self.ctx.check(lib().pcd_associate_evaluate_batch_dev(
+            self._h, C.c_void_p(d_p), C.c_void_p(d_range) if d_range else None, C.c_void_p(d_opt_num) if d_opt_num else None,
+            C.byref(sw) if sw is not None else None, C.c_int64(n), C.c_int(variant), C.c_double(weights[0]), C.c_double(weights[1]),
+            C.c_double(weights[2]), C.byref(out), C.c_void_p(d_r), C.c_void_p(d_J) if d_J else None,
+            C.c_void_p(d_sum) if d_sum else None, C.c_void_p(stream)), "pcd_associate_evaluate_batch_dev")
+
     def associate_dev(self, d_p, d_range, d_opt_num, sweep, n, variant, out_ptrs, stream=0):
         """out_ptrs: dict field -> device pointer (int)."""
         allf = ("idx", "accepted", "type", "rgb", "xyz", "abcd", "dist", "angle")

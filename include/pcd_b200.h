@@ -177,6 +177,12 @@ PCD_API int pcd_associate_evaluate_batch(pcd_cloud* cloud, const double* p_xyz, 
                                          double w_proj, double w_icp, double w_ground, const pcd_assoc_out* out,
                                          double* r, double* J, double* sum_sq);
 
+/* Device-pointer form of the fused pass (one record kernel writes the record fields, r, J and the partial sums). */
+PCD_API int pcd_associate_evaluate_batch_dev(pcd_cloud* cloud, const double* d_p_xyz, const double* d_range,
+                                             const int32_t* d_opt_num, const pcd_range_sweep* sweep, int64_t n, int variant,
+                                             double w_proj, double w_icp, double w_ground, const pcd_assoc_out* d_out,
+                                             double* d_r, double* d_J, double* d_sum_sq, void* stream);
+
 /* MatchVariablePoint2LidarPoint (src/optim/bundle_adjustment.cc:288-350): per point, among its
  * candidates cand[cand_start[i] .. cand_start[i+1]) (6 doubles each, track order) choose min
  * |v.n|/(|n||v|); outputs a Proj record (dist = point-to-plane).  found: uint8[n]. */

@@ -217,6 +217,32 @@ def test_associate_evaluate_fused_pass(scene, orc, pcd, ctx):
     assert np.array_equal(r3, r[acc]) and np.array_equal(J3, J[acc], equal_nan=True)
 
 
+def test_associate_evaluate_device_pointers(scene, orc, pcd, ctx):
+    """pcd_associate_evaluate_batch_dev (what bench.py times) == the host-pointer fused pass == oracle."""
+    import torch
+    q, on = scene["q"], scene["opt_num"]
+    n = len(q)
+    W = (10.0, 1000.0, 10000.0)
+    d_q = torch.from_numpy(q).cuda(); d_on = torch.from_numpy(on.astype(np.int32)).cuda()
+    o = {"idx": torch.empty(n, dtype=torch.int32, device="cuda"), "accepted": torch.empty(n, dtype=torch.uint8, device="cuda"),
+         "type": torch.empty(n, dtype=torch.uint8, device="cuda"), "abcd": torch.empty((n, 4), dtype=torch.float64, device="cuda")}
+    d_r = torch.empty(n, dtype=torch.float64, device="cuda"); d_J = torch.empty((n, 3), dtype=torch.float64, device="cuda")
+    d_s = torch.zeros(1, dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    scene["cloud"].associate_evaluate_dev(d_q.data_ptr(), 0, d_on.data_ptr(), (1.5, 0.2, 0.1), n, pcd.ASSOC_GLOBAL, W,
+                                          {k: v.data_ptr() for k, v in o.items()}, d_r.data_ptr(), d_J.data_ptr(), d_s.data_ptr(), st)
+    torch.cuda.synchronize()
+    rec, r, J, s = scene["cloud"].associate_evaluate(q, W, opt_num=on, sweep=(1.5, 0.2, 0.1), variant=pcd.ASSOC_GLOBAL)
+    assert np.array_equal(o["accepted"].cpu().numpy(), rec["accepted"]) and np.array_equal(o["idx"].cpu().numpy(), rec["idx"])
+    assert np.array_equal(d_r.cpu().numpy(), r) and np.array_equal(d_J.cpu().numpy(), J)
+    assert d_s.item() == s
+    want = scene["tree"].associate(q, orc.search_range(on), variant=1)
+    acc = want["accepted"].astype(bool)
+    w = np.where(want["type"] == 2, W[2], W[1])
+    ro, Jo = orc.resjac(q[acc], want["abcd"][acc], w[acc])
+    assert _close(r[acc], ro) and _close(J[acc], Jo) and _close(s, float(np.sum(ro * ro)), 1e-9)
+
+
 def test_match_proj(ctx, orc):
     rng = np.random.default_rng(11)
     n = 3000
