@@ -31,8 +31,8 @@ import __graft_entry__ as entry  # noqa: E402
 
 ALG_BYTES_NN = 260.0       # 12 B query + 8 B result + one 15-point leaf x 16 B
 # dram__bytes_read.sum + dram__bytes_write.sum of k_nn_search + k_nn_far from the one `ncu --set full` capture of the
-# default workload (profiles/r01_ncu_nn_v5_summary.txt: 3.768 + 0.866 + 1.063 + 0.079 GB for 16 M queries)
-NCU_TRAFFIC_NN_SWEEP50M = 5.776e9
+# default workload (profiles/r01_ncu_nn_v6_summary.txt: 3.709 + 0.777 + 0.710 + 0.071 GB for 16 M queries)
+NCU_TRAFFIC_NN_SWEEP50M = 5.267e9
 ALG_BYTES_RECORD = 56.0
 ALG_BYTES_RESJAC = 96.0
 WEIGHTS = (10.0, 1000.0, 10000.0)          # proj / icp / icp_ground (src/controllers/incremental_mapper.h:74-78)
@@ -57,8 +57,9 @@ def parse_args():
     ap.add_argument("--cloud", type=int, default=0, help="override cloud size")
     ap.add_argument("--queries", type=int, default=0, help="override queries per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather"],
-                    help="N > 1: all-gather the r / J blocks to every rank (default) or gather them to rank 0")
+    ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather", "p2p"],
+                    help="N > 1: NCCL all-gather of the r / J blocks to every rank, NCCL gather to rank 0, or p2p: pushes into "
+                         "every peer's symmetric buffer by copy engines over NVLink")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (query-count sweeps only; the default line carries it)")
     ap.add_argument("--zbuf-scale", type=float, default=1.0, help="depth_image_scale of the depth-projection leg (reference default 0.2)")
     ap.add_argument("--zbuf-images", type=int, default=6, help="images per GPU of the depth-projection leg (0 = skip)")
@@ -156,8 +157,10 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
                        "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
                        "parallelism": f"queries sharded x{world}, cloud+index replicated",
                        "exchange": "none (1 GPU)" if world == 1 else
-                       f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J fp64 blocks (32 B/query) + "
-                       "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass"}}
+                       (f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J fp64 blocks (32 B/query) + "
+                        "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass") if args.exchange != "p2p" else
+                       ("per pass: r and J fp64 blocks (32 B/query) pushed into every peer's symmetric-memory buffer by copy engines over "
+                        "NVLink + signal barrier + all_reduce of sum r^2, on side streams overlapping the next pass")}}
 
 
 def cpu_pass(orc, tree, q, rng, threads):
@@ -334,7 +337,9 @@ def run_b200(args):
     d_rb = [d_r, torch.empty_like(d_r)] if world > 1 else [d_r]
     d_Jb = [d_J, torch.empty_like(d_J)] if world > 1 else [d_J]
     shard = load_shard()
-    gather = shard.Exchange(Q, dev, root=0 if args.exchange == "gather" else None) if world > 1 else None
+    gather = None
+    if world > 1:
+        gather = shard.PeerExchange(Q, dev) if args.exchange == "p2p" else shard.Exchange(Q, dev, root=0 if args.exchange == "gather" else None)
     step_no = [0]
     flush = None if Q * 24 > 126e6 * 2 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
@@ -395,6 +400,19 @@ def run_b200(args):
     ev_end = torch.cuda.Event(enable_timing=True); ev_end.record()
     barrier()
     gpu_ms = evs[0][0].elapsed_time(ev_end) if flush is None else sum(a.elapsed_time(b) for a, b in evs)
+    exchange_ok = None
+    if gather is not None:                      # the gathered blocks of the last pass must be every rank's blocks
+        r_all, J_all, _ = gather.wait()
+        torch.cuda.synchronize()
+        lb = (step_no[0] - 1) & 1
+        chk = torch.stack([d_rb[lb].nan_to_num().sum(), d_Jb[lb].nan_to_num().sum()])
+        dist.all_reduce(chk, op=dist.ReduceOp.SUM)
+        if r_all.numel() > 0:
+            mine = bool(torch.equal(r_all[rank * Q:(rank + 1) * Q], d_rb[lb])) and bool(torch.equal(J_all[rank * Q:(rank + 1) * Q], d_Jb[lb]))
+            tot = torch.stack([r_all.nan_to_num().sum(), J_all.nan_to_num().sum()])
+            exchange_ok = mine and bool(torch.allclose(tot, chk, rtol=1e-9))
+        else:
+            exchange_ok = True
     launches = ctx.launches - launches0
     ktime = {k: ctx.kernel_time(getattr(pcd, k)) for k in ("K_NN_KEYSORT", "K_NN_SEARCH", "K_NN_FAR", "K_ASSOC_RECORD")}
     ctx.profile(False)
@@ -464,6 +482,8 @@ def run_b200(args):
         nn_avg_s = 1e-3 * nn_ms / max(nn_n, 1)
         achieved = ALG_BYTES_NN * Q / nn_avg_s / 1e9
         line["config"]["passes_per_step"] = passes
+        if exchange_ok is not None:
+            line["exchange_verified"] = exchange_ok
         line.update({"value": passes * Q * world / (ms_step * 1e-3), "ms_per_step": ms_step, "gpu_launches": int(launches),
                      "clocks": clocks,
                      "e2e": None if args.no_e2e else {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
@@ -472,7 +492,7 @@ def run_b200(args):
                      "roofline": {"bound": "hbm", "kernel": "k_nn_search + k_nn_far (timed together)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                   "frac": achieved / peak,
                                   "traffic": NCU_TRAFFIC_NN_SWEEP50M if (args.workload == "sweep50m" and Q == 16_000_000 and n_cloud == 50_000_000) else None,
-                                  "traffic_source": "profiles/r01_ncu_nn_v5_summary.txt (bytes per launch pair)", "peak_source": peak_src,
+                                  "traffic_source": "profiles/r01_ncu_nn_v6_summary.txt (bytes per launch pair)", "peak_source": peak_src,
                                   "algorithmic_bytes_per_query": ALG_BYTES_NN, "queries_per_launch": Q,
                                   "avg_launch_ms": 1e3 * nn_avg_s, "launches_timed": int(nn_n)},
                      "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktime.items()},

@@ -96,6 +96,76 @@ class Exchange:
         return self.r_all, self.J_all, self.stats
 
 
+class PeerExchange:
+    """The same exchange step written over NVLink peer memory instead of NCCL's all-gather kernels.
+
+    Every rank owns a symmetric receive buffer (torch symmetric memory: each peer's buffer is mapped into the local
+    address space).  After a pass, a rank pushes its r [Q] and J [Q, 3] blocks straight into its slot of every peer's
+    buffer with device-to-device copies on per-peer side streams -- copy engines over NVLink / NVSwitch, no SM taken
+    from the search kernels that run the next pass at the same time -- then joins a signal-pad barrier, after which
+    every rank holds every block.  Two receive buffers alternate, so a consumer has a whole pass to read one.
+    The fp64 statistics still go through a (tiny) NCCL all-reduce.
+    """
+
+    def __init__(self, q_per_rank, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.q = int(q_per_rank)
+        dev = torch.device(device)
+        n = self.world * self.q
+        self.recv, self.hdl, self.peer_views = [], [], []
+        for _ in range(2):
+            t = symm.empty(4 * n, dtype=torch.float64, device=dev)
+            h = symm.rendezvous(t, group=self.group)
+            self.recv.append(t); self.hdl.append(h)
+            self.peer_views.append([h.get_buffer(p, (4 * n,), torch.float64) for p in range(self.world)])
+        self.stats = torch.zeros(3, dtype=torch.float64, device=dev)
+        self.main = torch.cuda.Stream(device=dev, priority=-1)
+        self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(self.world)]
+        self.events = [torch.cuda.Event() for _ in range(2)]
+        self.pending = [False, False]
+        self.last = 0
+
+    def views(self, buf):
+        n = self.world * self.q
+        return self.recv[buf][:n], self.recv[buf][n:].view(n, 3)
+
+    def start(self, r, J, stats, buf=0):
+        n, q, me = self.world * self.q, self.q, self.rank
+        cur = torch.cuda.current_stream()
+        Jf = J.reshape(-1)
+        for k in range(self.world):                      # own slot first, then the peers in ring order
+            p = (me + k) % self.world
+            st = self.streams[p]
+            st.wait_stream(cur)
+            with torch.cuda.stream(st):
+                dst = self.peer_views[buf][p]
+                dst[me * q:(me + 1) * q].copy_(r, non_blocking=True)
+                dst[n + 3 * me * q:n + 3 * (me + 1) * q].copy_(Jf, non_blocking=True)
+        self.main.wait_stream(cur)
+        for st in self.streams:
+            self.main.wait_stream(st)
+        with torch.cuda.stream(self.main):
+            self.hdl[buf].barrier(channel=0)             # every rank's pushes of this pass have landed
+            self.stats.copy_(stats)
+            dist.all_reduce(self.stats, op=dist.ReduceOp.SUM, group=self.group)
+            self.events[buf].record(self.main)
+        self.pending[buf] = True
+        self.last = buf
+
+    def wait_buffer(self, buf):
+        if self.pending[buf]:
+            torch.cuda.current_stream().wait_event(self.events[buf])
+            self.pending[buf] = False
+
+    def wait(self):
+        torch.cuda.current_stream().wait_stream(self.main)
+        r_all, J_all = self.views(self.last)
+        return r_all, J_all, self.stats
+
+
 def gather_ragged(local, group=None):
     """All-gather of per-rank 1-D/2-D tensors whose first dimension differs (result sets of a ragged shard)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
