@@ -47,7 +47,7 @@ __device__ __forceinline__ void normalize_plane(const double l[6], double abcd[4
 struct EvalDev { double wp, wi, wg; double* r; double* J; double* partial; };
 
 template <bool FUSED_EVAL>
-__global__ void __launch_bounds__(256) k_assoc_record(const float4* __restrict__ aos, const double* __restrict__ p, const int32_t* __restrict__ nn_idx,
+__global__ void __launch_bounds__(256) k_assoc_record(const float4* __restrict__ aos, const double* __restrict__ p, const int32_t* nn_idx /* may alias o.idx */,
                                const double* __restrict__ range, const int32_t* __restrict__ opt_num, pcd_range_sweep sw,
                                int64_t n, int variant, pcd_assoc_out o, unsigned long long* __restrict__ counters, EvalDev ev) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -220,7 +220,7 @@ static int associate_dev_impl(pcd_cloud* cloud, const double* d_p, const double*
   int rc = pcd::nn_search_dev(cloud, d_p, rr, fixed, on, sweep, n, d_idx, nullptr, false, st);   // k_assoc_record applies the fp64 range test
   if (rc) return rc;
   pcd_range_sweep sw = sweep ? *sweep : pcd_range_sweep{0, 0, 0};
-  pcd_assoc_out o = *d_out; o.idx = nullptr;   // idx already written by the search (or private)
+  pcd_assoc_out o = *d_out;   // o.idx (= the search's output array when given) is rewritten: -1 for a neighbour beyond the range
   const int nb = pcd_blocks(n, 256);
   pcd::ProfScope ps(ctx, PCD_K_ASSOC_RECORD, st);
   if (ev) {

@@ -174,6 +174,22 @@ def test_associate_matches_reference_loops(scene, orc, variant):
     assert np.array_equal(got["abcd"][acc], want["abcd"][acc])
 
 
+def test_associate_idx_is_minus_one_beyond_range(scene, orc):
+    """include/pcd_b200.h: idx = -1 when there is no neighbour within the search range (the reference finds the
+    farther point and drops it at bundle_adjustment.cc:400); the unbounded NN of those queries is still >= 0."""
+    q = scene["q"]
+    rng = np.full(len(q), 0.05)
+    got = scene["cloud"].associate(q, range_=rng, variant=0)
+    oi, _ = scene["tree"].nn(q)
+    l = scene["world"][oi, 0:3].astype(np.float64)
+    v = l - q
+    dist = np.sqrt(v[:, 0] ** 2 + (v[:, 1] ** 2 + v[:, 2] ** 2))
+    beyond = dist > rng
+    assert beyond.sum() > 1000 and (~beyond).sum() > 1000
+    assert (got["idx"][beyond] == -1).all() and not got["accepted"][beyond].any()
+    assert np.array_equal(got["idx"][~beyond], oi[~beyond])
+
+
 def test_associate_opt_num_sweep_equals_explicit_range(scene, orc):
     a = scene["cloud"].associate(scene["q"][:20000], opt_num=scene["opt_num"][:20000], sweep=(1.5, 0.2, 0.1), variant=1)
     b = scene["cloud"].associate(scene["q"][:20000], range_=orc.search_range(scene["opt_num"][:20000]), variant=1)
