@@ -57,6 +57,10 @@ def parse_args():
     ap.add_argument("--cloud", type=int, default=0, help="override cloud size")
     ap.add_argument("--queries", type=int, default=0, help="override queries per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange-wire", default="f64", choices=["f64", "f32"],
+                    help="N>1: format of the residual/Jacobian blocks on the wire. f64 (default): as computed, 32 B/query. "
+                         "f32: rounded to a float4 by pcd_pack_blocks_f32_dev first, 16 B/query (relative error <= 2^-24, "
+                         "stated separately from the fp64 result)")
     ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather", "p2p"],
                     help="N > 1: NCCL all-gather of the r / J blocks to every rank, NCCL gather to rank 0, or p2p: pushes into "
                          "every peer's symmetric buffer by copy engines over NVLink")
@@ -157,7 +161,8 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
                        "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
                        "parallelism": f"queries sharded x{world}, cloud+index replicated",
                        "exchange": "none (1 GPU)" if world == 1 else
-                       (f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J fp64 blocks (32 B/query) + "
+                       (f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J "
+                        f"{'fp64 blocks (32 B/query)' if args.exchange_wire == 'f64' else 'blocks rounded to float4 by k_pack_blocks_f32 (16 B/query; fp64 results stay on the producer)'} + "
                         "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass") if args.exchange != "p2p" else
                        ("per pass: r and J fp64 blocks (32 B/query) pushed into every peer's symmetric-memory buffer by copy engines over "
                         "NVLink + signal barrier + all_reduce of sum r^2, on side streams overlapping the next pass")}}
@@ -339,7 +344,13 @@ def run_b200(args):
     shard = load_shard()
     gather = None
     if world > 1:
-        gather = shard.PeerExchange(Q, dev) if args.exchange == "p2p" else shard.Exchange(Q, dev, root=0 if args.exchange == "gather" else None)
+        if args.exchange == "p2p":
+            gather = shard.PeerExchange(Q, dev)
+        else:
+            def pack(r_, J_, out, st):
+                ctx.pack_blocks_f32_dev(r_.data_ptr(), J_.data_ptr(), Q, out.data_ptr(), st)
+            gather = shard.Exchange(Q, dev, root=0 if args.exchange == "gather" else None, wire=args.exchange_wire,
+                                    pack=pack if args.exchange_wire == "f32" else None)
     step_no = [0]
     flush = None if Q * 24 > 126e6 * 2 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
@@ -405,11 +416,13 @@ def run_b200(args):
         r_all, J_all, _ = gather.wait()
         torch.cuda.synchronize()
         lb = (step_no[0] - 1) & 1
-        chk = torch.stack([d_rb[lb].nan_to_num().sum(), d_Jb[lb].nan_to_num().sum()])
+        wire_t = torch.float32 if (args.exchange_wire == "f32" and args.exchange != "p2p") else torch.float64
+        sent_r, sent_J = d_rb[lb].to(wire_t), d_Jb[lb].to(wire_t)          # what this rank put on the wire
+        chk = torch.stack([sent_r.double().nan_to_num().sum(), sent_J.double().nan_to_num().sum()])
         dist.all_reduce(chk, op=dist.ReduceOp.SUM)
         if r_all.numel() > 0:
-            mine = bool(torch.equal(r_all[rank * Q:(rank + 1) * Q], d_rb[lb])) and bool(torch.equal(J_all[rank * Q:(rank + 1) * Q], d_Jb[lb]))
-            tot = torch.stack([r_all.nan_to_num().sum(), J_all.nan_to_num().sum()])
+            mine = bool(torch.equal(r_all[rank * Q:(rank + 1) * Q], sent_r)) and bool(torch.equal(J_all[rank * Q:(rank + 1) * Q], sent_J))
+            tot = torch.stack([r_all.double().nan_to_num().sum(), J_all.double().nan_to_num().sum()])
             exchange_ok = mine and bool(torch.allclose(tot, chk, rtol=1e-9))
         else:
             exchange_ok = True

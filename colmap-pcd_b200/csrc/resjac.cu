@@ -106,6 +106,14 @@ __global__ void k_weights(const uint8_t* __restrict__ type, int64_t n, double wp
   w[i] = t == PCD_TYPE_PROJ ? wp : (t == PCD_TYPE_ICP ? wi : (t == PCD_TYPE_ICP_GROUND ? wg : 0.0));
 }
 
+// fp32 wire format of one residual block for the multi-GPU exchange: {r, J0, J1, J2} rounded to nearest float
+// (relative error <= 2^-24, inside the path's 1e-5 tolerance; the fp64 blocks stay on the producing GPU).
+__global__ void k_pack_blocks_f32(const double* __restrict__ r, const double* __restrict__ J, int64_t n, float4* __restrict__ out) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = make_float4((float)r[i], (float)J[3 * i], (float)J[3 * i + 1], (float)J[3 * i + 2]);
+}
+
 __global__ void k_filter(const double* __restrict__ p, const double* __restrict__ l, const uint8_t* __restrict__ type, int64_t n,
                          double max_proj, double max_icp, uint8_t* __restrict__ erase, unsigned long long* __restrict__ cnt) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -137,6 +145,17 @@ int pcd_residual_jacobian_batch_dev(pcd_ctx* ctx, const double* d_p, const doubl
   pcd::k_resjac<<<nb, pcd::RJ_THREADS, 0, st>>>(d_p, (const double4*)d_abcd, d_w, n, d_r, d_J, partial);
   PCD_LAUNCH_CHECK(ctx);
   if (d_sum_sq) { pcd::k_sum_partials<<<1, 256, 0, st>>>(partial, nb, d_sum_sq); PCD_LAUNCH_CHECK(ctx); }
+  return PCD_OK;
+}
+
+int pcd_pack_blocks_f32_dev(pcd_ctx* ctx, const double* d_r, const double* d_J, int64_t n, float* d_out, void* stream) {
+  if (!ctx || n < 0 || (n > 0 && (!d_r || !d_J || !d_out))) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_pack_blocks_f32_dev: bad argument");
+  if (((uintptr_t)d_out & 15) != 0) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_pack_blocks_f32_dev: d_out must be 16-byte aligned");
+  if (n == 0) return PCD_OK;
+  DeviceGuard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  pcd::k_pack_blocks_f32<<<pcd_blocks(n, 256), 256, 0, st>>>(d_r, d_J, n, (float4*)d_out);
+  PCD_LAUNCH_CHECK(ctx);
   return PCD_OK;
 }
 

@@ -130,6 +130,11 @@ class Context:
                                                    C.c_double(w_icp), C.c_double(w_ground), C.c_void_p(d_w),
                                                    C.c_void_p(stream)), "pcd_weights_from_type_dev")
 
+    def pack_blocks_f32_dev(self, d_r, d_J, n, d_out, stream=0):
+        """fp32 wire format {r, J0, J1, J2} of n residual blocks (device pointers), for the multi-GPU exchange."""
+        self.check(lib().pcd_pack_blocks_f32_dev(self._h, C.c_void_p(d_r), C.c_void_p(d_J), C.c_int64(n), C.c_void_p(d_out),
+                                                 C.c_void_p(stream)), "pcd_pack_blocks_f32_dev")
+
     # -- a19 --------------------------------------------------------------------------------
     def residual_jacobian(self, p, abcd, w, jac=True, want_sum=True, out=None):
         p, abcd, w = _f64(p, 3), _f64(abcd, 4), _f64(w).ravel()

@@ -40,47 +40,64 @@ class Exchange:
     the caller alternates between two (r, J) output buffers and calls wait_buffer(b) before overwriting buffer b.
     """
 
-    def __init__(self, q_per_rank, device, group=None, root=0):
+    def __init__(self, q_per_rank, device, group=None, root=0, wire="f64", pack=None):
         """root = r: gather to rank r only (the consumer is the host-side solver of one process; the other ranks
-        send their 32 B/query once and receive nothing).  root = None: all-gather, every rank gets every block."""
+        send their blocks once and receive nothing).  root = None: all-gather, every rank gets every block.
+        wire = "f64": r and J travel as computed (32 B/query).  wire = "f32": `pack(r, J, out, stream_ptr)` (the
+        library's pcd_pack_blocks_f32_dev) rounds each block to a float4 {r, J0, J1, J2} first -- 16 B/query on the
+        wire, relative error <= 2^-24; the gathered views are float32 and the fp64 blocks stay with their producer."""
+        if wire not in ("f64", "f32") or (wire == "f32" and pack is None):
+            raise ValueError("Exchange: wire is 'f64' or 'f32' (the latter needs the pack callable)")
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.group = group
         self.root = root
+        self.wire, self.pack = wire, pack
         self.q = int(q_per_rank)
         dev = torch.device(device)
         self.cuda = dev.type == "cuda"
         full = self.world * self.q if (root is None or self.rank == root) else 0
-        self.r_all = torch.empty(full, dtype=torch.float64, device=dev)
-        self.J_all = torch.empty((full, 3), dtype=torch.float64, device=dev)
+        if wire == "f32":
+            self.w_local = [torch.empty((self.q, 4), dtype=torch.float32, device=dev) for _ in range(2)]
+            self.w_all = torch.empty((full, 4), dtype=torch.float32, device=dev)
+            self.r_all, self.J_all = self.w_all[:, 0], self.w_all[:, 1:4]
+        else:
+            self.r_all = torch.empty(full, dtype=torch.float64, device=dev)
+            self.J_all = torch.empty((full, 3), dtype=torch.float64, device=dev)
         self.stats = torch.zeros(3, dtype=torch.float64, device=dev)
         # high priority: the collective's CTAs must not queue behind the search kernels' 60 k-block grids
         self.stream = torch.cuda.Stream(device=dev, priority=-1) if self.cuda else None
         self.events = [torch.cuda.Event() for _ in range(2)] if self.cuda else None
         self.pending = [False, False]
 
-    def _run(self, r, J, stats):
+    def _run(self, r, J, stats, buf=0):
+        parts = [(self.r_all, r), (self.J_all, J)]
+        if self.wire == "f32":
+            w = self.w_local[buf]
+            self.pack(r, J, w, self.stream.cuda_stream if self.cuda else 0)
+            parts = [(self.w_all, w)]
         if self.world > 1:
-            if self.root is None:
-                dist.all_gather_into_tensor(self.r_all, r, group=self.group)
-                dist.all_gather_into_tensor(self.J_all, J, group=self.group)
-            else:
-                here = self.rank == self.root
-                dist.gather(r, list(self.r_all.split(self.q)) if here else None, dst=self.root, group=self.group)
-                dist.gather(J, list(self.J_all.split(self.q)) if here else None, dst=self.root, group=self.group)
+            for dst, src in parts:
+                if self.root is None:
+                    dist.all_gather_into_tensor(dst, src, group=self.group)
+                else:
+                    here = self.rank == self.root
+                    dist.gather(src, list(dst.split(self.q)) if here else None, dst=self.root, group=self.group)
             self.stats.copy_(stats)
             dist.all_reduce(self.stats, op=dist.ReduceOp.SUM, group=self.group)
         else:
-            self.r_all.copy_(r); self.J_all.copy_(J); self.stats.copy_(stats)
+            for dst, src in parts:
+                dst.copy_(src)
+            self.stats.copy_(stats)
 
     def start(self, r, J, stats, buf=0):
         """r, J: this rank's outputs of the pass just enqueued; stats: fp64 [3]."""
         if not self.cuda:
-            self._run(r, J, stats)
+            self._run(r, J, stats, buf)
             return
         self.stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.stream):
-            self._run(r, J, stats)
+            self._run(r, J, stats, buf)
             self.events[buf].record(self.stream)
         self.pending[buf] = True
 

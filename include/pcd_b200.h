@@ -197,6 +197,10 @@ PCD_API int pcd_residual_jacobian_batch(pcd_ctx* ctx, const double* p_xyz, const
                                         int64_t n, double* r, double* J, double* sum_sq);
 PCD_API int pcd_residual_jacobian_batch_dev(pcd_ctx* ctx, const double* d_p_xyz, const double* d_abcd, const double* d_w,
                                             int64_t n, double* d_r, double* d_J, double* d_sum_sq, void* stream);
+/* fp32 wire format of the residual blocks for the multi-GPU exchange (north_star: "fp32 paths stated separately";
+ * no reference counterpart).  d_out[4n] = {r, J0, J1, J2} per constraint, each rounded to nearest float; d_out is
+ * 16-byte aligned.  The fp64 blocks are unchanged; this is a transport format only. */
+PCD_API int pcd_pack_blocks_f32_dev(pcd_ctx* ctx, const double* d_r, const double* d_J, int64_t n, float* d_out, void* stream);
 /* north_star extension (no reference counterpart): the point expressed through
  * a camera, p_w = R(q)^T (p_c - t).  J_pose[7n] = d r / d (qw qx qy qz tx ty tz). */
 PCD_API int pcd_residual_pose_jacobian_batch(pcd_ctx* ctx, const double* p_cam, const double* qvec, const double* tvec,

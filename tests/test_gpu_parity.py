@@ -259,6 +259,27 @@ def test_associate_evaluate_device_pointers(scene, orc, pcd, ctx):
     assert _close(r[acc], ro) and _close(J[acc], Jo) and _close(s, float(np.sum(ro * ro)), 1e-9)
 
 
+def test_pack_blocks_f32_wire_format(ctx):
+    """pcd_pack_blocks_f32_dev: {r, J0, J1, J2} rounded to nearest float (the multi-GPU exchange's fp32 wire format);
+    bit-exact against numpy's float64 -> float32 conversion, NaN / inf / denormal-range values included."""
+    import torch
+    rng = np.random.default_rng(5)
+    n = 100_003
+    r = rng.normal(0, 50, n); J = rng.normal(0, 1e3, (n, 3))
+    r[:6] = [0.0, -0.0, np.nan, np.inf, 1e-46, 3.5e38]; J[:3, 1] = [np.nan, -np.inf, 1e-40]
+    d_r = torch.from_numpy(r).cuda(); d_J = torch.from_numpy(J).cuda()
+    d_o = torch.full((n, 4), -1.0, dtype=torch.float32, device="cuda")
+    ctx.pack_blocks_f32_dev(d_r.data_ptr(), d_J.data_ptr(), n, d_o.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    with np.errstate(over="ignore"):
+        want = np.concatenate([r[:, None], J], 1).astype(np.float32)
+    got = d_o.cpu().numpy()
+    assert np.array_equal(got, want, equal_nan=True)                      # NaN payloads may differ between cvt.rn and the host
+    assert np.array_equal(np.signbit(got[~np.isnan(want)]), np.signbit(want[~np.isnan(want)]))
+    ok = np.isfinite(want) & (np.abs(want) > 1e-30)
+    assert np.all(np.abs(want[ok] - np.concatenate([r[:, None], J], 1)[ok]) <= 2.0 ** -24 * np.abs(want[ok]) * 1.0000001)
+
+
 def test_match_proj(ctx, orc):
     rng = np.random.default_rng(11)
     n = 3000

@@ -48,6 +48,13 @@ def _worker(rank, world, port, n_q, out_dir):
         if rank == 0:
             assert torch.equal(got[None], got[0])
         allb = got[None]
+        # fp32 wire format: the same exchange on rounded float4 blocks (the CUDA pack kernel's arithmetic, restated)
+        ex = shard.Exchange(hi - lo, "cpu", root=None, wire="f32",
+                            pack=lambda r_, J_, out, st: out.copy_(torch.cat([r_[:, None], J_], 1).to(torch.float32)))
+        ex.start(torch.from_numpy(r), torch.from_numpy(J), local, 1)
+        r32, J32, stats32 = ex.wait()
+        assert r32.dtype == torch.float32 and torch.equal(torch.cat([r32[:, None], J32], 1), allb.to(torch.float32))
+        assert torch.equal(stats32, stats)
         stats = stats.clone()
     else:                                 # ragged shards
         allb = shard.gather_ragged(block)

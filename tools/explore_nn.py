@@ -1,6 +1,7 @@
 """GPU exploration: k_nn_search time vs cell size, x sub-division and lanes-per-query (run under gpurun).
 
-usage: explore_nn.py n_cloud n_queries cells xsubs groups [radius|unbounded] [chunks]
+usage: explore_nn.py n_cloud n_queries cells xsubs groups [radius|unbounded]
+(EXPLORE_ENVS="A=1;A=2" repeats the sweep once per ;-separated set of environment knobs)
 """
 import os
 import sys
@@ -20,7 +21,6 @@ cells = [float(x) for x in (arg[2] or "0.125,0.25,0.5").split(",")]
 xsubs = [int(x) for x in (arg[3] or "1,4").split(",")]
 groups = [int(x) for x in (arg[4] or "1,2").split(",")]
 mode = arg[5] or "radius"
-chunks = [int(x) for x in (arg[6] or "0").split(",")]
 ctx = pcd.Context(0)
 raw, _ = synth.make_cloud(n_cloud, seed=synth.SEED0 + 4)
 cloud = pcd.Cloud(ctx, raw, direction_trans=True)
@@ -35,7 +35,7 @@ d_idx = torch.empty(Q, dtype=torch.int32, device="cuda")
 d_d2 = torch.empty(Q, dtype=torch.float32, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
 ref = None
-envs = [e for e in os.environ.get("EXPLORE_ENVS", "").split(";")] or [""]     # e.g. "PCD_B200_NN_FLAT=0;PCD_B200_NN_FLAT=1"
+envs = [e for e in os.environ.get("EXPLORE_ENVS", "").split(";")] or [""]     # e.g. "PCD_B200_SORT_SKIP=0;PCD_B200_SORT_SKIP=4"
 for env in envs:
   for kv in filter(None, env.split(",")):
     os.environ[kv.split("=")[0]] = kv.split("=")[1]
@@ -49,9 +49,8 @@ for env in envs:
               print(f"cell {cell} xs {xs}: {e}")
               continue
           for g in groups:
-              for ch in chunks:
+              if True:
                   os.environ["PCD_B200_NN_K1"] = str(g)
-                  os.environ["PCD_B200_NN_CHUNK"] = str(ch)
                   rp = d_rad.data_ptr() if d_rad is not None else 0
                   for _ in range(2):
                       cloud.nn_dev(d_q.data_ptr(), rp, Q, d_idx.data_ptr(), d_d2.data_ptr(), st)
@@ -68,5 +67,5 @@ for env in envs:
                   if ref is None:
                       ref = res
                   same = bool(np.array_equal(ref, res))
-                  print(f"cell {cell:7.4f} xs {xs:2d} cells {info['n_cells']:>11d} K1 {g:2d} chunk {ch:4d}: search {ms / n:8.3f} ms  "
+                  print(f"cell {cell:7.4f} xs {xs:2d} cells {info['n_cells']:>11d} K1 {g:2d}: search {ms / n:8.3f} ms  "
                         f"(far {fs / n:6.3f}) keysort {ks / n:6.3f} ms  {Q / (ms / n) / 1e3:8.1f} Mq/s  hits {(res >= 0).mean():.3f} same={same}", flush=True)
