@@ -207,7 +207,7 @@ void pcd_cloud_destroy(pcd_cloud* c) {
   DeviceGuard g(c->ctx->device);
   cudaDeviceSynchronize();
   cudaFree(c->aos); cudaFree(c->grid_pts); cudaFree(c->cell_start); cudaFree(c->occ);
-  cudaFree(c->sub_keys); cudaFree(c->sub_start); cudaFree(c->sub_pts);
+  cudaFree(c->sub_keys); cudaFree(c->sub_start); cudaFree(c->sub_pts); cudaFree(c->sub_seg);
   delete c;
 }
 
@@ -385,6 +385,21 @@ int pcd_index_info(const pcd_cloud* c, float* cell_size, int32_t dims[3], float 
   return PCD_OK;
 }
 
+namespace pcd {
+// segments per cell (entry `runs` is the zero that closes the exclusive sum)
+__global__ void k_seg_count(const uint32_t* __restrict__ start, int runs, uint32_t* __restrict__ nseg) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c > runs) return;
+  nseg[c] = c == runs ? 0u : (start[c + 1] - start[c] + SUBMAP_SEG - 1) / SUBMAP_SEG;
+}
+__global__ void k_seg_fill(const uint32_t* __restrict__ start, const uint32_t* __restrict__ segoff, int runs, uint2* __restrict__ seg) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= runs) return;
+  uint32_t o = segoff[c], b = start[c];
+  for (uint32_t e = start[c + 1]; b < e; b += SUBMAP_SEG) seg[o++] = make_uint2((uint32_t)c, b);
+}
+}  // namespace pcd
+
 // ---------------------------------------------------------------------------------------
 // a9  PcdProj::BuildSubMap (src/lidar/pcd_projection.cc:223-255)
 // ---------------------------------------------------------------------------------------
@@ -396,12 +411,15 @@ int pcd_submap_build(pcd_cloud* c, const pcd_proj_options* opt) {
   DeviceGuard g(ctx->device);
   cudaStream_t st = ctx->stream;
   const int64_t n = c->n;
-  if (c->has_submap) { cudaFree(c->sub_keys); cudaFree(c->sub_start); cudaFree(c->sub_pts); c->sub_keys = nullptr; c->sub_start = nullptr; c->sub_pts = nullptr; c->has_submap = false; }
+  if (c->has_submap) {
+    cudaFree(c->sub_keys); cudaFree(c->sub_start); cudaFree(c->sub_pts); cudaFree(c->sub_seg);
+    c->sub_keys = nullptr; c->sub_start = nullptr; c->sub_pts = nullptr; c->sub_seg = nullptr; c->sub_nseg = 0; c->has_submap = false;
+  }
   c->opt = *opt;
   if (n == 0) {
     PCD_CUDA(ctx, cudaMalloc(&c->sub_keys, 16)); PCD_CUDA(ctx, cudaMalloc(&c->sub_start, 8)); PCD_CUDA(ctx, cudaMalloc(&c->sub_pts, 16));
     PCD_CUDA(ctx, cudaMemsetAsync(c->sub_start, 0, 8, st));
-    c->sub_cells = 0; c->has_submap = true;
+    c->sub_cells = 0; c->sub_nseg = 0; c->has_submap = true;
     return PCD_OK;
   }
   // bbox (recomputed so the sub-map does not depend on the NN index)
@@ -459,6 +477,23 @@ int pcd_submap_build(pcd_cloud* c, const pcd_proj_options* opt) {
   PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
   PCD_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, d_counts, c->sub_start, runs + 1, st));
   k_sub_decode<<<pcd_blocks(runs, 256), 256, 0, st>>>(d_uniq, runs, k0[0], k0[1], k0[2], c->sub_keys);
+  PCD_LAUNCH_CHECK(ctx);
+  // work list of the projection: every cell cut into segments of at most SUBMAP_SEG points
+  uint32_t* d_nseg = d_counts;                               // the counts are consumed; reuse as segments per cell
+  PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)(runs + 1)));
+  uint32_t* d_segoff = ctx->vals.as<uint32_t>();
+  pcd::k_seg_count<<<pcd_blocks(runs + 1, 256), 256, 0, st>>>(c->sub_start, runs, d_nseg);
+  PCD_LAUNCH_CHECK(ctx);
+  tmp = 0;
+  PCD_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp, d_nseg, d_segoff, runs + 1, st));
+  PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+  PCD_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, d_nseg, d_segoff, runs + 1, st));
+  uint32_t nseg = 0;
+  PCD_CUDA(ctx, cudaMemcpyAsync(&nseg, d_segoff + runs, 4, cudaMemcpyDeviceToHost, st));
+  PCD_CUDA(ctx, cudaStreamSynchronize(st));
+  c->sub_nseg = nseg;
+  PCD_CUDA(ctx, cudaMalloc(&c->sub_seg, sizeof(uint2) * (size_t)(nseg > 0 ? nseg : 1)));
+  pcd::k_seg_fill<<<pcd_blocks(runs, 256), 256, 0, st>>>(c->sub_start, d_segoff, runs, c->sub_seg);
   PCD_LAUNCH_CHECK(ctx);
   PCD_CUDA(ctx, cudaStreamSynchronize(st));
   k64a.release(); k64b.release();

@@ -66,8 +66,11 @@ struct SubmapView {
   const uint32_t* start;        // n_cells + 1
   const float4* pts;            // x, y, z, original index; insertion order inside a cell
   int64_t n_cells;
+  const uint2* seg;             // work list of the projection: {cell, first point}, at most SUBMAP_SEG points each
+  int64_t n_seg;
   float len, height, width;
 };
+constexpr uint32_t SUBMAP_SEG = 128;   // points per work item: bounds the serial work of one warp in k_project
 
 }  // namespace pcd
 
@@ -133,7 +136,8 @@ struct pcd_cloud {
   int32_t* sub_keys = nullptr;
   uint32_t* sub_start = nullptr;
   float4* sub_pts = nullptr;
-  int64_t sub_cells = 0;
+  uint2* sub_seg = nullptr;
+  int64_t sub_cells = 0, sub_nseg = 0;
 };
 
 #define PCD_FAIL(ctx_, code_, ...)                                   \

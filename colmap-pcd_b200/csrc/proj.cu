@@ -87,7 +87,11 @@ static void make_params(const pcd_image& im, const pcd_proj_options& o, const do
 }
 
 // feature pixel = (xy * scale).cast<int>() (truncation), bounds-checked (pcd_projection.cc:35-36)
-__global__ void k_feature_mask(const double* __restrict__ xy, int64_t n, ImgParams P, uint32_t* __restrict__ mask, int64_t* __restrict__ px_out) {
+// mask: one bit per pixel; summ: the OR of MASK_ROWS consecutive mask rows, so that a splat skips feature-free
+// row groups with one load per word instead of MASK_ROWS.
+constexpr int MASK_ROWS_LOG2 = 3, MASK_ROWS = 1 << MASK_ROWS_LOG2;
+__global__ void k_feature_mask(const double* __restrict__ xy, int64_t n, ImgParams P, uint32_t* __restrict__ mask,
+                               uint32_t* __restrict__ summ, int64_t* __restrict__ px_out) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   int u = (int)(xy[2 * i] * P.scale), v = (int)(xy[2 * i + 1] * P.scale);
@@ -95,18 +99,21 @@ __global__ void k_feature_mask(const double* __restrict__ xy, int64_t n, ImgPara
   if (!(u < 0 || u >= P.w || v < 0 || v >= P.h)) {
     px = (int64_t)v * P.w + u;
     atomicOr(&mask[(int64_t)v * P.words + (u >> 5)], 1u << (u & 31));
+    atomicOr(&summ[(int64_t)(v >> MASK_ROWS_LOG2) * P.words + (u >> 5)], 1u << (u & 31));
   }
   px_out[i] = px;
 }
 
 template <bool DENSE>
 __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, const uint32_t* __restrict__ mask,
-                                                 unsigned long long* __restrict__ zbuf, unsigned long long* __restrict__ stats) {
+                                                 const uint32_t* __restrict__ summ, unsigned long long* __restrict__ zbuf, unsigned long long* __restrict__ stats) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   unsigned long long n_pts = 0, n_px = 0, n_cells = 0;
-  for (int64_t c = warp; c < sm.n_cells; c += nwarps) {
+  for (int64_t s = warp; s < sm.n_seg; s += nwarps) {
+    const uint2 sg = __ldg(&sm.seg[s]);
+    const int64_t c = sg.x;
     // a11: cell centre (idx*len, idy*height, idz*width) against the five planes, float32, left to right
     float x = (float)sm.keys[3 * c] * sm.len, y = (float)sm.keys[3 * c + 1] * sm.height, z = (float)sm.keys[3 * c + 2] * sm.width;
     bool in = true;
@@ -118,8 +125,8 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
       in = in && (v <= 0.0f);
     }
     if (!in) continue;
-    if (lane == 0) n_cells++;
-    const uint32_t b = sm.start[c], e = sm.start[c + 1];
+    const uint32_t b = sg.y, e = min(b + SUBMAP_SEG, sm.start[c + 1]);
+    if (lane == 0 && b == sm.start[c]) n_cells++;            // a cell counts once, with its first segment
     for (uint32_t j = b + lane; j < e; j += 32) {
       float4 pw = __ldg(&sm.pts[j]);
       float pc[3];
@@ -159,18 +166,22 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
         }
       } else {
         const int wa = ua >> 5, wb = ub >> 5;
-        for (int v = va; v <= vb; v++) {
-          const uint32_t* mrow = mask + (int64_t)v * P.words;
+        for (int vg = va >> MASK_ROWS_LOG2; vg <= (vb >> MASK_ROWS_LOG2); vg++) {
+          const uint32_t* srow = summ + (int64_t)vg * P.words;
           for (int wd = wa; wd <= wb; wd++) {
-            uint32_t bits = __ldg(&mrow[wd]);
-            if (!bits) continue;
+            uint32_t any = __ldg(&srow[wd]);
+            if (!any) continue;
             int lo = max(ua - (wd << 5), 0), hi = min(ub - (wd << 5), 31);
-            uint32_t m = (hi == 31 ? 0xffffffffu : ((1u << (hi + 1)) - 1u)) & ~((1u << lo) - 1u);
-            bits &= m;
-            while (bits) {
-              int bpos = __ffs(bits) - 1; bits &= bits - 1;
-              unsigned long long* px = zbuf + (int64_t)v * P.w + (wd << 5) + bpos;
-              if (packed < *px) atomicMin(px, packed);
+            const uint32_t m = (hi == 31 ? 0xffffffffu : ((1u << (hi + 1)) - 1u)) & ~((1u << lo) - 1u);
+            if (!(any & m)) continue;
+            const int v1 = min(vb, (vg << MASK_ROWS_LOG2) + MASK_ROWS - 1);
+            for (int v = max(va, vg << MASK_ROWS_LOG2); v <= v1; v++) {
+              uint32_t bits = __ldg(&mask[(int64_t)v * P.words + wd]) & m;
+              while (bits) {
+                int bpos = __ffs(bits) - 1; bits &= bits - 1;
+                unsigned long long* px = zbuf + (int64_t)v * P.w + (wd << 5) + bpos;
+                if (packed < *px) atomicMin(px, packed);
+              }
             }
           }
         }
@@ -236,26 +247,29 @@ static int project_one(pcd_cloud* c, const pcd_image* img, const double coef[4],
   if (P.w <= 0 || P.h <= 0 || (int64_t)P.w * P.h > ((int64_t)1 << 28)) PCD_FAIL(ctx, PCD_E_INVALID, "bad scaled image size %d x %d", P.w, P.h);
   const int64_t npx = (int64_t)P.w * P.h;
   PCD_CUDA(ctx, ctx->zbuf.ensure(8 * (size_t)npx));
-  PCD_CUDA(ctx, ctx->sel_buf.ensure(4 * (size_t)P.words * P.h + 8 * (size_t)(n_feat > 0 ? n_feat : 1) + 64));
+  const size_t mask_words = (size_t)P.words * ((size_t)P.h + (size_t)((P.h + MASK_ROWS - 1) >> MASK_ROWS_LOG2));   // mask + row-group summary
+  PCD_CUDA(ctx, ctx->sel_buf.ensure(4 * mask_words + 8 * (size_t)(n_feat > 0 ? n_feat : 1) + 64));
   unsigned long long* zb = ctx->zbuf.as<unsigned long long>();
   uint32_t* mask = ctx->sel_buf.as<uint32_t>();
-  int64_t* d_px = (int64_t*)((char*)ctx->sel_buf.p + (((size_t)4 * P.words * P.h + 63) & ~(size_t)63));
+  uint32_t* summ = mask + (size_t)P.words * P.h;
+  int64_t* d_px = (int64_t*)((char*)ctx->sel_buf.p + ((4 * mask_words + 63) & ~(size_t)63));
   PCD_CUDA(ctx, cudaMemsetAsync(zb, 0xff, 8 * (size_t)npx, st));
-  PCD_CUDA(ctx, cudaMemsetAsync(mask, 0, 4 * (size_t)P.words * P.h, st));
+  PCD_CUDA(ctx, cudaMemsetAsync(mask, 0, 4 * mask_words, st));
   if (n_feat > 0) {
-    k_feature_mask<<<pcd_blocks(n_feat, 256), 256, 0, st>>>(d_feat, n_feat, P, mask, d_px);
+    k_feature_mask<<<pcd_blocks(n_feat, 256), 256, 0, st>>>(d_feat, n_feat, P, mask, summ, d_px);
     PCD_LAUNCH_CHECK(ctx);
   }
   SubmapView sm;
   sm.keys = c->sub_keys; sm.start = c->sub_start; sm.pts = c->sub_pts; sm.n_cells = c->sub_cells;
+  sm.seg = c->sub_seg; sm.n_seg = c->sub_nseg;
   sm.len = c->opt.submap_length; sm.height = c->opt.submap_height; sm.width = c->opt.submap_width;
   if (c->sub_cells > 0 && (dense || n_feat > 0)) {
-    int64_t warps = c->sub_cells;
+    int64_t warps = c->sub_nseg;
     int blocks = (int)((warps + 7) / 8);
     int cap = ctx->sm_count * 16; if (blocks > cap) blocks = cap;
     ProfScope ps(ctx, PCD_K_PROJECT, st);
-    if (dense) k_project<true><<<blocks, 256, 0, st>>>(sm, P, mask, zb, d_stats);
-    else k_project<false><<<blocks, 256, 0, st>>>(sm, P, mask, zb, d_stats);
+    if (dense) k_project<true><<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats);
+    else k_project<false><<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats);
     PCD_LAUNCH_CHECK(ctx);
   }
   if (n_feat > 0 && d_widx) {
