@@ -387,16 +387,16 @@ int pcd_index_info(const pcd_cloud* c, float* cell_size, int32_t dims[3], float 
 
 namespace pcd {
 // segments per cell (entry `runs` is the zero that closes the exclusive sum)
-__global__ void k_seg_count(const uint32_t* __restrict__ start, int runs, uint32_t* __restrict__ nseg) {
+__global__ void k_seg_count(const uint32_t* __restrict__ start, int runs, uint32_t SEG, uint32_t* __restrict__ nseg) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c > runs) return;
-  nseg[c] = c == runs ? 0u : (start[c + 1] - start[c] + SUBMAP_SEG - 1) / SUBMAP_SEG;
+  nseg[c] = c == runs ? 0u : (start[c + 1] - start[c] + SEG - 1) / SEG;
 }
-__global__ void k_seg_fill(const uint32_t* __restrict__ start, const uint32_t* __restrict__ segoff, int runs, uint2* __restrict__ seg) {
+__global__ void k_seg_fill(const uint32_t* __restrict__ start, const uint32_t* __restrict__ segoff, int runs, uint32_t SEG, uint2* __restrict__ seg) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= runs) return;
   uint32_t o = segoff[c], b = start[c];
-  for (uint32_t e = start[c + 1]; b < e; b += SUBMAP_SEG) seg[o++] = make_uint2((uint32_t)c, b);
+  for (uint32_t e = start[c + 1]; b < e; b += SEG) seg[o++] = make_uint2((uint32_t)c, b);
 }
 }  // namespace pcd
 
@@ -482,7 +482,9 @@ int pcd_submap_build(pcd_cloud* c, const pcd_proj_options* opt) {
   uint32_t* d_nseg = d_counts;                               // the counts are consumed; reuse as segments per cell
   PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)(runs + 1)));
   uint32_t* d_segoff = ctx->vals.as<uint32_t>();
-  pcd::k_seg_count<<<pcd_blocks(runs + 1, 256), 256, 0, st>>>(c->sub_start, runs, d_nseg);
+  c->sub_seglen = pcd::SUBMAP_SEG;
+  if (const char* e = getenv("PCD_B200_SUBMAP_SEG")) { int v = atoi(e); if (v >= 32 && v <= 65536) c->sub_seglen = (uint32_t)v; }   // tuning knob
+  pcd::k_seg_count<<<pcd_blocks(runs + 1, 256), 256, 0, st>>>(c->sub_start, runs, c->sub_seglen, d_nseg);
   PCD_LAUNCH_CHECK(ctx);
   tmp = 0;
   PCD_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp, d_nseg, d_segoff, runs + 1, st));
@@ -493,7 +495,7 @@ int pcd_submap_build(pcd_cloud* c, const pcd_proj_options* opt) {
   PCD_CUDA(ctx, cudaStreamSynchronize(st));
   c->sub_nseg = nseg;
   PCD_CUDA(ctx, cudaMalloc(&c->sub_seg, sizeof(uint2) * (size_t)(nseg > 0 ? nseg : 1)));
-  pcd::k_seg_fill<<<pcd_blocks(runs, 256), 256, 0, st>>>(c->sub_start, d_segoff, runs, c->sub_seg);
+  pcd::k_seg_fill<<<pcd_blocks(runs, 256), 256, 0, st>>>(c->sub_start, d_segoff, runs, c->sub_seglen, c->sub_seg);
   PCD_LAUNCH_CHECK(ctx);
   PCD_CUDA(ctx, cudaStreamSynchronize(st));
   k64a.release(); k64b.release();

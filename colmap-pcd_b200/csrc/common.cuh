@@ -66,11 +66,12 @@ struct SubmapView {
   const uint32_t* start;        // n_cells + 1
   const float4* pts;            // x, y, z, original index; insertion order inside a cell
   int64_t n_cells;
-  const uint2* seg;             // work list of the projection: {cell, first point}, at most SUBMAP_SEG points each
+  const uint2* seg;             // work list of the projection: {cell, first point}, at most seg_len points each
   int64_t n_seg;
+  uint32_t seg_len;
   float len, height, width;
 };
-constexpr uint32_t SUBMAP_SEG = 128;   // points per work item: bounds the serial work of one warp in k_project
+constexpr uint32_t SUBMAP_SEG = 64;    // default points per work item: bounds the serial work of one warp in k_project
 
 }  // namespace pcd
 
@@ -138,6 +139,7 @@ struct pcd_cloud {
   float4* sub_pts = nullptr;
   uint2* sub_seg = nullptr;
   int64_t sub_cells = 0, sub_nseg = 0;
+  uint32_t sub_seglen = pcd::SUBMAP_SEG;
 };
 
 #define PCD_FAIL(ctx_, code_, ...)                                   \

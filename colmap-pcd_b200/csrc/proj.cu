@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
       in = in && (v <= 0.0f);
     }
     if (!in) continue;
-    const uint32_t b = sg.y, e = min(b + SUBMAP_SEG, sm.start[c + 1]);
+    const uint32_t b = sg.y, e = min(b + sm.seg_len, sm.start[c + 1]);
     if (lane == 0 && b == sm.start[c]) n_cells++;            // a cell counts once, with its first segment
     for (uint32_t j = b + lane; j < e; j += 32) {
       float4 pw = __ldg(&sm.pts[j]);
@@ -261,7 +261,7 @@ static int project_one(pcd_cloud* c, const pcd_image* img, const double coef[4],
   }
   SubmapView sm;
   sm.keys = c->sub_keys; sm.start = c->sub_start; sm.pts = c->sub_pts; sm.n_cells = c->sub_cells;
-  sm.seg = c->sub_seg; sm.n_seg = c->sub_nseg;
+  sm.seg = c->sub_seg; sm.n_seg = c->sub_nseg; sm.seg_len = c->sub_seglen;
   sm.len = c->opt.submap_length; sm.height = c->opt.submap_height; sm.width = c->opt.submap_width;
   if (c->sub_cells > 0 && (dense || n_feat > 0)) {
     int64_t warps = c->sub_nseg;

@@ -423,6 +423,22 @@ def test_project_images_batch_equals_single(scene, proj_scene, pcd, synth):
         assert np.array_equal(widx[fs[k]:fs[k + 1]], a) and np.array_equal(wr[fs[k]:fs[k + 1]], b)
 
 
+def test_zbuffer_invariant_to_segment_length(scene, proj_scene, pcd, ctx, monkeypatch):
+    """The projection's work list cuts every sub-map cell into segments (common.cuh SUBMAP_SEG); winners, the dense map
+    and the counters (a selected cell counts once, however many segments it has) must not depend on the cut."""
+    ps = proj_scene
+    n = len(scene["world"])
+    assert n / ps["sub"].n_cells > 32                  # cells hold many points: short segments really split them
+    cam = ps["cams"][0]
+    im = pcd.Image.make(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"])
+    zo, counters, n_sel = ps["sub"].project(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"], ps["coef"])
+    for seg in ("32", "65536"):
+        monkeypatch.setenv("PCD_B200_SUBMAP_SEG", seg)
+        cl = pcd.Cloud(ctx, scene["world"]); cl.build_submap(ps["opt_g"])
+        _, _, z, stats = cl.project_image(im, ps["coef"], None, dense=True)
+        assert np.array_equal(z, zo) and stats[0] == n_sel and stats[1] == counters[0] and stats[2] == counters[1]
+
+
 def test_zbuffer_full_res_and_empty_frustum(scene, orc, synth, pcd, ctx):
     # depth_image_scale = 1 at 1920x1080 (config 4 shape), plus a camera looking away from everything
     opt_g = pcd.ProjOptions.default(depth_image_scale=1.0); opt_o = orc.ProjOptions.default(depth_image_scale=1.0)
