@@ -104,6 +104,42 @@ __global__ void k_feature_mask(const double* __restrict__ xy, int64_t n, ImgPara
   px_out[i] = px;
 }
 
+// a12/a13 for one cloud point: camera frame, pinhole + DistortOpenCV, splat rectangle clipped to the image.
+// Returns true when the rectangle is not empty; n_pts / n_px are the reference's counters.
+__device__ __forceinline__ bool point_rect(const ImgParams& P, const float4 pw, unsigned long long& packed, int& ua, int& ub,
+                                           int& va, int& vb, unsigned long long& n_pts, unsigned long long& n_px) {
+  float pc[3];
+#pragma unroll
+  for (int i = 0; i < 3; i++) pc[i] = (P.R[3 * i] * pw.x + (P.R[3 * i + 1] * pw.y + P.R[3 * i + 2] * pw.z)) + P.t[i];
+  if (pc[2] < 0) return false;
+  float dist = pc[2];
+  if ((double)dist < P.min_lidar) return false;
+  double fx = P.cam[0], fy = P.cam[1], cx = P.cam[2], cy = P.cam[3];
+  double u_ori = fx * (double)__fdiv_rn(pc[0], pc[2]) + cx;
+  double v_ori = fy * (double)__fdiv_rn(pc[1], pc[2]) + cy;
+  // DistortOpenCV
+  double xn = (u_ori - cx) / fx, yn = (v_ori - cy) / fy;
+  double r2 = xn * xn + yn * yn;
+  double Ra = 1. + P.cam[4] * r2 + P.cam[5] * r2 * r2;
+  double Tx = 2. * P.cam[6] * xn * yn + P.cam[7] * (r2 + 2. * xn * xn);
+  double Ty = P.cam[6] * (r2 + 2. * yn * yn) + 2. * P.cam[7] * xn * yn;
+  double ud = (xn * Ra * 1.0 + Tx) * fx + cx, vd = (yn * Ra * 1.0 + Ty) * fy + cy;
+  double ru = round(ud * P.scale), rv = round(vd * P.scale);
+  if (!(fabs(ru) < 1e9) || !(fabs(rv) < 1e9)) return false;
+  int u0 = (int)ru, v0 = (int)rv;
+  int sx, sy;
+  if ((double)dist <= P.min_proj_dist) { sx = (int)P.max_x; sy = (int)P.max_y; }
+  else if ((double)dist > P.min_proj_dist) { sx = (int)(P.coef[0] * (double)dist + P.coef[1]); sy = (int)(P.coef[2] * (double)dist + P.coef[3]); }
+  else return false;
+  float range = sqrtf(pc[0] * pc[0] + (pc[1] * pc[1] + pc[2] * pc[2]));
+  packed = ((unsigned long long)__float_as_uint(range) << 32) | __float_as_uint(pw.w);
+  n_pts++;
+  ua = max(u0 - sx, 0); ub = min(u0 + sx, P.w - 1); va = max(v0 - sy, 0); vb = min(v0 + sy, P.h - 1);
+  if (ua > ub || va > vb) return false;
+  n_px += (unsigned long long)(ub - ua + 1) * (unsigned long long)(vb - va + 1);
+  return true;
+}
+
 template <bool DENSE>
 __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, const uint32_t* __restrict__ mask,
                                                  const uint32_t* __restrict__ summ, unsigned long long* __restrict__ zbuf, unsigned long long* __restrict__ stats) {
@@ -127,44 +163,28 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
     if (!in) continue;
     const uint32_t b = sg.y, e = min(b + sm.seg_len, sm.start[c + 1]);
     if (lane == 0 && b == sm.start[c]) n_cells++;            // a cell counts once, with its first segment
-    for (uint32_t j = b + lane; j < e; j += 32) {
-      float4 pw = __ldg(&sm.pts[j]);
-      float pc[3];
-#pragma unroll
-      for (int i = 0; i < 3; i++) pc[i] = (P.R[3 * i] * pw.x + (P.R[3 * i + 1] * pw.y + P.R[3 * i + 2] * pw.z)) + P.t[i];
-      if (pc[2] < 0) continue;
-      float dist = pc[2];
-      if ((double)dist < P.min_lidar) continue;
-      double fx = P.cam[0], fy = P.cam[1], cx = P.cam[2], cy = P.cam[3];
-      double u_ori = fx * (double)__fdiv_rn(pc[0], pc[2]) + cx;
-      double v_ori = fy * (double)__fdiv_rn(pc[1], pc[2]) + cy;
-      // DistortOpenCV
-      double xn = (u_ori - cx) / fx, yn = (v_ori - cy) / fy;
-      double r2 = xn * xn + yn * yn;
-      double Ra = 1. + P.cam[4] * r2 + P.cam[5] * r2 * r2;
-      double Tx = 2. * P.cam[6] * xn * yn + P.cam[7] * (r2 + 2. * xn * xn);
-      double Ty = P.cam[6] * (r2 + 2. * yn * yn) + 2. * P.cam[7] * xn * yn;
-      double ud = (xn * Ra * 1.0 + Tx) * fx + cx, vd = (yn * Ra * 1.0 + Ty) * fy + cy;
-      double ru = round(ud * P.scale), rv = round(vd * P.scale);
-      if (!(fabs(ru) < 1e9) || !(fabs(rv) < 1e9)) continue;
-      int u0 = (int)ru, v0 = (int)rv;
-      int sx, sy;
-      if ((double)dist <= P.min_proj_dist) { sx = (int)P.max_x; sy = (int)P.max_y; }
-      else if ((double)dist > P.min_proj_dist) { sx = (int)(P.coef[0] * (double)dist + P.coef[1]); sy = (int)(P.coef[2] * (double)dist + P.coef[3]); }
-      else continue;
-      float range = sqrtf(pc[0] * pc[0] + (pc[1] * pc[1] + pc[2] * pc[2]));
-      unsigned long long packed = ((unsigned long long)__float_as_uint(range) << 32) | __float_as_uint(pw.w);
-      n_pts++;
-      int ua = max(u0 - sx, 0), ub = min(u0 + sx, P.w - 1), va = max(v0 - sy, 0), vb = min(v0 + sy, P.h - 1);
-      if (ua > ub || va > vb) continue;
-      n_px += (unsigned long long)(ub - ua + 1) * (unsigned long long)(vb - va + 1);
+    for (uint32_t j0 = b; j0 < e; j0 += 32) {                // warp-uniform trip count
+      const uint32_t j = j0 + lane;
+      unsigned long long packed = 0;
+      int ua = 0, ub = -1, va = 0, vb = -1;
+      const bool rect = j < e && point_rect(P, __ldg(&sm.pts[j]), packed, ua, ub, va, vb, n_pts, n_px);
       if (DENSE) {
-        for (int v = va; v <= vb; v++) {
-          unsigned long long* row = zbuf + (int64_t)v * P.w;
-          for (int u = ua; u <= ub; u++)
-            if (packed < row[u]) atomicMin(&row[u], packed);
+        // the warp splats its points one after the other, lanes side by side along the pixel rows: one warp-wide
+        // atomic touches 32 consecutive 8-byte words instead of 32 rows
+        unsigned todo = __ballot_sync(0xffffffffu, rect);
+        while (todo) {
+          const int src = __ffs(todo) - 1; todo &= todo - 1;
+          const unsigned long long pk = __shfl_sync(0xffffffffu, packed, src);
+          const int a0 = __shfl_sync(0xffffffffu, ua, src), a1 = __shfl_sync(0xffffffffu, ub, src);
+          const int r0 = __shfl_sync(0xffffffffu, va, src), r1 = __shfl_sync(0xffffffffu, vb, src);
+          const int W = a1 - a0 + 1, tot = W * (r1 - r0 + 1);
+          for (int t = lane; t < tot; t += 32) {
+            const int dv = t / W, du = t - dv * W;
+            unsigned long long* px = zbuf + (int64_t)(r0 + dv) * P.w + (a0 + du);
+            if (pk < *px) atomicMin(px, pk);
+          }
         }
-      } else {
+      } else if (rect) {
         const int wa = ua >> 5, wb = ub >> 5;
         for (int vg = va >> MASK_ROWS_LOG2; vg <= (vb >> MASK_ROWS_LOG2); vg++) {
           const uint32_t* srow = summ + (int64_t)vg * P.words;

@@ -12,6 +12,8 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as entry
 
 pcd = entry.package()
+if os.environ.get("EXPLORE_LIB"):          # compare against another build of the library
+    pcd.LIB_PATH = os.path.abspath(os.environ["EXPLORE_LIB"])
 synth = entry._load("pcd_synth", os.path.join(entry.PKG, "synth.py"))
 arg = sys.argv[1:] + [""] * 4
 n_cloud = int(arg[0] or 20_000_000)
@@ -39,11 +41,14 @@ for seg in segs:
     dt = time.perf_counter() - t0
     k_ms, k_n = ctx.kernel_time(pcd.K_PROJECT)
     ctx.profile(False)
+    ctx.profile(True)
     t0 = time.perf_counter()
     _, _, z, dstats = cloud.project_image(imgs[0], coef, None, dense=True)
     dd = time.perf_counter() - t0
+    dk_ms, _ = ctx.kernel_time(pcd.K_PROJECT)
+    ctx.profile(False)
     if ref is None:
         ref = (widx.copy(), z.copy())
     same = bool(np.array_equal(ref[0], widx)) and bool(np.array_equal(ref[1], z))
-    print(f"seg {seg:8d}: k_project {k_ms / max(k_n, 1):7.3f} ms/image  {n_img / dt:8.1f} images/s  dense {1e3 * dd:7.2f} ms "
-          f"({dstats[2] / dd / 1e9:6.1f} G atomics/s)  cells {n_cells}  same={same}", flush=True)
+    print(f"seg {seg:8d}: k_project {k_ms / max(k_n, 1):7.3f} ms/image  {n_img / dt:8.1f} images/s  dense {1e3 * dd:7.2f} ms, kernel {dk_ms:6.3f} ms "
+          f"({dstats[2] / (1e-3 * dk_ms) / 1e9:6.1f} G atomics/s in the kernel)  cells {n_cells}  same={same}", flush=True)
