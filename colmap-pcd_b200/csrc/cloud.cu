@@ -235,7 +235,8 @@ int pcd_index_build(pcd_cloud* c, float cell_size) {
   DeviceGuard g(ctx->device);
   cudaStream_t st = ctx->stream;
   const int64_t n = c->n;
-  if (c->has_index) { cudaFree(c->grid_pts); cudaFree(c->cell_start); cudaFree(c->occ); c->grid_pts = nullptr; c->cell_start = nullptr; c->occ = nullptr; c->has_index = false; }
+  cudaFree(c->grid_pts); cudaFree(c->cell_start); cudaFree(c->occ);      // also what a failed build left behind
+  c->grid_pts = nullptr; c->cell_start = nullptr; c->occ = nullptr; c->has_index = false;
   pcd::GridView& G = c->grid;
   memset(&G, 0, sizeof G);
   if (n == 0) {
@@ -411,10 +412,10 @@ int pcd_submap_build(pcd_cloud* c, const pcd_proj_options* opt) {
   DeviceGuard g(ctx->device);
   cudaStream_t st = ctx->stream;
   const int64_t n = c->n;
-  if (c->has_submap) {
-    cudaFree(c->sub_keys); cudaFree(c->sub_start); cudaFree(c->sub_pts); cudaFree(c->sub_seg);
-    c->sub_keys = nullptr; c->sub_start = nullptr; c->sub_pts = nullptr; c->sub_seg = nullptr; c->sub_nseg = 0; c->has_submap = false;
-  }
+  // also after a build that failed half way: whatever it allocated is released before the next attempt
+  cudaFree(c->sub_keys); cudaFree(c->sub_start); cudaFree(c->sub_pts); cudaFree(c->sub_seg);
+  c->sub_keys = nullptr; c->sub_start = nullptr; c->sub_pts = nullptr; c->sub_seg = nullptr;
+  c->sub_cells = 0; c->sub_nseg = 0; c->has_submap = false;
   c->opt = *opt;
   if (n == 0) {
     PCD_CUDA(ctx, cudaMalloc(&c->sub_keys, 16)); PCD_CUDA(ctx, cudaMalloc(&c->sub_start, 8)); PCD_CUDA(ctx, cudaMalloc(&c->sub_pts, 16));
