@@ -11,6 +11,13 @@
 #include <vector>
 #include <sstream>
 #include <fstream>
+#include <atomic>
+#include <charconv>
+#include <thread>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include "../../include/pcd_b200.h"
 
 namespace pcd { void set_global_error(const std::string& s); }
@@ -57,6 +64,55 @@ int slot_of(const std::string& n) {
 }
 
 int fail(int code, const std::string& msg) { pcd::set_global_error(msg); return code; }
+
+// Splits [0, n) over the host threads (at most 16, at least `grain` items each) and runs fn(t, lo, hi).
+template <class F>
+void parallel_ranges(int64_t n, int64_t grain, F fn) {
+  unsigned hw = std::thread::hardware_concurrency();
+  int64_t T = hw ? (hw > 16 ? 16 : hw) : 1;
+  if (T > (n + grain - 1) / grain) T = (n + grain - 1) / grain;
+  if (T <= 1) { fn(0, (int64_t)0, n); return; }
+  std::vector<std::thread> th;
+  for (int64_t t = 0; t < T; t++) th.emplace_back(fn, (int)t, n * t / T, n * (t + 1) / T);
+  for (auto& x : th) x.join();
+}
+
+// Read-only mapping of a whole file.
+struct FileMap {
+  const char* p = nullptr; size_t len = 0;
+  bool open(const char* path) {
+    int fd = ::open(path, O_RDONLY);
+    if (fd < 0) return false;
+    struct stat st;
+    if (fstat(fd, &st) != 0) { ::close(fd); return false; }
+    len = (size_t)st.st_size;
+    if (len > 0) {
+      void* m = mmap(nullptr, len, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (m == MAP_FAILED) { ::close(fd); return false; }
+      p = (const char*)m;
+    }
+    ::close(fd);
+    return true;
+  }
+  ~FileMap() { if (p) munmap((void*)p, len); }
+};
+
+// One decimal token of an ASCII vertex line -> double, with strtod's value (the caller narrows to float).
+// Returns the position after the token, or nullptr when there is none.
+const char* parse_number(const char* s, const char* end, double& v) {
+  while (s < end && (*s == ' ' || *s == '\t' || *s == '\r')) s++;
+  if (s >= end) return nullptr;
+  const char* t = (*s == '+') ? s + 1 : s;
+  auto r = std::from_chars(t, end, v);
+  if (r.ec == std::errc() && r.ptr > t) return r.ptr;
+  // out-of-range values, hexadecimal floats ...: let strtod decide on a bounded copy of the token
+  char tok[128]; size_t k = 0;
+  while (s + k < end && k + 1 < sizeof tok && s[k] != ' ' && s[k] != '\t' && s[k] != '\r') { tok[k] = s[k]; k++; }
+  tok[k] = 0;
+  char* e = nullptr;
+  v = strtod(tok, &e);
+  return e == tok ? nullptr : s + (e - tok);
+}
 
 }  // namespace
 
@@ -105,35 +161,81 @@ extern "C" int pcd_ply_read(const char* path, float** aos8, int64_t* n_out) {
     stride += props[i].size;
   }
   if (!(have_xyz[0] && have_xyz[1] && have_xyz[2])) return fail(PCD_E_IO, std::string(path) + ": vertex has no x/y/z");
+  const std::streamoff body_off = (std::streamoff)f.tellg();
+  f.close();
+  FileMap fm;
+  if (!fm.open(path) || body_off < 0 || (size_t)body_off > fm.len) return fail(PCD_E_IO, std::string("Couldn't read file ") + path);
+  const char* body = fm.p + body_off;
+  const size_t body_len = fm.len - (size_t)body_off;
+  if (!ascii && (stride == 0 || (size_t)n > body_len / stride)) return fail(PCD_E_IO, std::string(path) + ": truncated vertex data");
   float* out = (float*)calloc((size_t)(n > 0 ? n : 1) * 8, sizeof(float));
   if (!out) return fail(PCD_E_NOMEM, "pcd_ply_read: out of memory");
+  const size_t np = props.size();
   if (ascii) {
-    for (int64_t i = 0; i < n; i++) {
-      if (!std::getline(f, line)) { free(out); return fail(PCD_E_IO, std::string(path) + ": truncated vertex data"); }
-      const char* s = line.c_str(); char* e = nullptr;
-      for (size_t k = 0; k < props.size(); k++) {
-        double v = strtod(s, &e);
-        if (e == s) { free(out); return fail(PCD_E_IO, std::string(path) + ": bad vertex line"); }
-        s = e;
-        if (slot[k] >= 0) out[8 * i + slot[k]] = (float)v;
-      }
+    // one vertex per line.  The body is cut into byte ranges at line ends; a first pass counts the lines of every
+    // range, so that the second pass knows which vertex each range starts with.
+    unsigned hw = std::thread::hardware_concurrency();
+    int T = hw ? (hw > 16 ? 16 : (int)hw) : 1;
+    if ((size_t)T > body_len / (1 << 20) + 1) T = (int)(body_len / (1 << 20) + 1);
+    std::vector<size_t> cut(T + 1);
+    cut[0] = 0; cut[T] = body_len;
+    for (int t = 1; t < T; t++) {
+      size_t c = body_len / T * t;
+      if (c < cut[t - 1]) c = cut[t - 1];
+      const void* nl = c < body_len ? memchr(body + c, '\n', body_len - c) : nullptr;
+      cut[t] = nl ? (size_t)((const char*)nl - body) + 1 : body_len;
     }
+    std::vector<int64_t> first(T + 1, 0);
+    {
+      std::vector<int64_t> cnt(T, 0);
+      std::vector<std::thread> th;
+      for (int t = 0; t < T; t++)
+        th.emplace_back([&, t] {
+          int64_t c = 0;
+          const char* q = body + cut[t]; const char* e = body + cut[t + 1];
+          while (q < e) { const void* nl = memchr(q, '\n', e - q); if (!nl) { c++; break; } c++; q = (const char*)nl + 1; }
+          cnt[t] = c;
+        });
+      for (auto& x : th) x.join();
+      for (int t = 0; t < T; t++) first[t + 1] = first[t] + cnt[t];
+    }
+    if (first[T] < n) { free(out); return fail(PCD_E_IO, std::string(path) + ": truncated vertex data"); }
+    std::atomic<int> bad(0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < T; t++)
+      th.emplace_back([&, t] {
+        const char* q = body + cut[t]; const char* e = body + cut[t + 1];
+        for (int64_t i = first[t]; i < first[t + 1] && i < n && q < e; i++) {
+          const void* nl = memchr(q, '\n', e - q);
+          const char* le_ = nl ? (const char*)nl : e;
+          const char* sp = q;
+          for (size_t k = 0; k < np; k++) {
+            double v;
+            sp = parse_number(sp, le_, v);
+            if (!sp) { bad.store(1); return; }
+            if (slot[k] >= 0) out[8 * i + slot[k]] = (float)v;
+          }
+          q = le_ + 1;
+        }
+      });
+    for (auto& x : th) x.join();
+    if (bad.load()) { free(out); return fail(PCD_E_IO, std::string(path) + ": bad vertex line"); }
   } else {
-    const int64_t chunk = 1 << 16;
-    std::vector<unsigned char> buf(stride * (size_t)chunk);
-    for (int64_t base = 0; base < n; base += chunk) {
-      int64_t m = (n - base < chunk) ? (n - base) : chunk;
-      f.read((char*)buf.data(), (std::streamsize)(stride * (size_t)m));
-      if ((size_t)f.gcount() != stride * (size_t)m) { free(out); return fail(PCD_E_IO, std::string(path) + ": truncated vertex data"); }
-      for (int64_t i = 0; i < m; i++) {
-        const unsigned char* b = buf.data() + stride * (size_t)i;
-        size_t off = 0;
-        for (size_t k = 0; k < props.size(); k++) {
-          if (slot[k] >= 0) out[8 * (base + i) + slot[k]] = read_bin(b + off, props[k]);
-          off += props[k].size;
+    bool all_f32 = true;
+    std::vector<size_t> offs(np);
+    { size_t off = 0; for (size_t k = 0; k < np; k++) { offs[k] = off; off += props[k].size; all_f32 = all_f32 && props[k].kind == 'f'; } }
+    const unsigned char* ub = (const unsigned char*)body;
+    parallel_ranges(n, 1 << 18, [&](int, int64_t lo, int64_t hi) {
+      for (int64_t i = lo; i < hi; i++) {
+        const unsigned char* b = ub + stride * (size_t)i;
+        float* o = out + 8 * i;
+        if (all_f32) {
+          for (size_t k = 0; k < np; k++) if (slot[k] >= 0) memcpy(o + slot[k], b + offs[k], 4);
+        } else {
+          for (size_t k = 0; k < np; k++) if (slot[k] >= 0) o[slot[k]] = read_bin(b + offs[k], props[k]);
         }
       }
-    }
+    });
   }
   *aos8 = out; *n_out = n;
   return PCD_OK;
@@ -146,13 +248,27 @@ extern "C" int pcd_ply_write(const char* path, const float* aos8, int64_t n, int
   fprintf(f, "ply\nformat %s 1.0\nelement vertex %lld\n", binary ? "binary_little_endian" : "ascii", (long long)n);
   fprintf(f, "property float x\nproperty float y\nproperty float z\n");
   fprintf(f, "property float normal_x\nproperty float normal_y\nproperty float normal_z\nend_header\n");
-  for (int64_t i = 0; i < n; i++) {
-    const float* p = aos8 + 8 * i;
-    float row[6] = {p[0], p[1], p[2], p[4], p[5], p[6]};
-    if (binary) fwrite(row, sizeof(float), 6, f);
-    else fprintf(f, "%.9g %.9g %.9g %.9g %.9g %.9g\n", row[0], row[1], row[2], row[3], row[4], row[5]);
+  bool ok = true;
+  if (binary) {
+    const int64_t chunk = 1 << 16;
+    std::vector<float> rows(6 * (size_t)chunk);
+    for (int64_t base = 0; base < n && ok; base += chunk) {
+      const int64_t m = n - base < chunk ? n - base : chunk;
+      for (int64_t i = 0; i < m; i++) {
+        const float* p = aos8 + 8 * (base + i);
+        float* r = rows.data() + 6 * i;
+        r[0] = p[0]; r[1] = p[1]; r[2] = p[2]; r[3] = p[4]; r[4] = p[5]; r[5] = p[6];
+      }
+      ok = fwrite(rows.data(), 6 * sizeof(float), (size_t)m, f) == (size_t)m;
+    }
+  } else {
+    for (int64_t i = 0; i < n && ok; i++) {
+      const float* p = aos8 + 8 * i;
+      ok = fprintf(f, "%.9g %.9g %.9g %.9g %.9g %.9g\n", p[0], p[1], p[2], p[4], p[5], p[6]) > 0;
+    }
   }
-  fclose(f);
+  ok = (fclose(f) == 0) && ok;
+  if (!ok) return fail(PCD_E_IO, std::string("write error on ") + path);
   return PCD_OK;
 }
 

@@ -80,6 +80,62 @@ def test_ply_io_host_only(pcd, small, tmp_path):
     assert a.shape == (2, 8) and np.array_equal(a[1, [0, 1, 2, 4, 5, 6]], [4, 5, 6, 0, 1, 0])
 
 
+def test_ply_reader_threaded_paths(pcd, tmp_path):
+    """The loader (a1, src/lidar/ply.cc:14) parses the vertex block on several host threads: byte ranges cut at line
+    ends for ASCII, index ranges for binary.  Every range boundary, line shape and token form must give the value a
+    single-threaded float(strtod(token)) gives; trailing elements are ignored; damage is an error, never a guess."""
+    rng = np.random.default_rng(3)
+    n = 300_000                                              # several MB of text: more than one byte range per thread pool
+    a = (rng.normal(0, 30, (n, 6)) * 10.0 ** rng.integers(-6, 6, (n, 1))).astype(np.float32)
+    a[::1000, 3] = np.nan; a[1::1000, 4] = np.inf; a[2::1000, 5] = -np.inf
+    fmts = ["%.9g", "%+.8e", "%.10f", "%r"]                  # lines of very different lengths, '+' signs, exponents
+    lines = []
+    for i in range(n):
+        f = fmts[i & 3]
+        lines.append(("\t" if i % 7 == 0 else " ").join((f % float(v)) if f != "%r" else repr(float(v)) for v in a[i]) + ("\r\n" if i % 5 == 0 else "\n"))
+    head = ("ply\nformat ascii 1.0\ncomment made by test\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
+            "property float normal_x\nproperty float normal_y\nproperty float normal_z\nelement face 1\n"
+            "property list uchar int vertex_indices\nend_header\n" % n)
+    path = tmp_path / "big_ascii.ply"
+    path.write_text(head + "".join(lines) + "3 0 1 2", newline="")     # a face after the vertices, no trailing newline
+    got = pcd.ply_read(str(path))
+    want = np.zeros((n, 8), np.float32)                      # what float(strtod(token)) gives, token by token
+    want[:, [0, 1, 2, 4, 5, 6]] = np.array([[float(t) for t in ln.split()] for ln in lines], dtype=np.float64).astype(np.float32)
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    assert np.array_equal(np.nan_to_num(got, nan=12345.0), np.nan_to_num(want, nan=12345.0))
+    assert np.array_equal(np.signbit(got), np.signbit(want))
+    # last vertex line without a newline at the end of the file
+    (tmp_path / "nonl.ply").write_text(head.replace("element face 1\nproperty list uchar int vertex_indices\n", "") + "".join(lines).rstrip("\r\n"), newline="")
+    assert np.array_equal(np.nan_to_num(pcd.ply_read(str(tmp_path / "nonl.ply")), nan=12345.0), np.nan_to_num(want, nan=12345.0))
+    # one vertex line short, and one damaged token deep inside the file
+    (tmp_path / "short.ply").write_text(head.replace("element face 1\nproperty list uchar int vertex_indices\n", "") + "".join(lines[:-1]), newline="")
+    with pytest.raises(pcd.PcdError, match="truncated"):
+        pcd.ply_read(str(tmp_path / "short.ply"))
+    broken = list(lines); broken[n - 12345] = "1 2 oops 4 5 6\n"
+    (tmp_path / "broken.ply").write_text(head + "".join(broken), newline="")
+    with pytest.raises(pcd.PcdError, match="bad vertex line"):
+        pcd.ply_read(str(tmp_path / "broken.ply"))
+    # binary little-endian with mixed property types and a trailing element; then the same file cut short
+    m = 600_000
+    rec = np.zeros(m, dtype=[("x", "<f8"), ("red", "u1"), ("y", "<f4"), ("z", "<f4"), ("nx", "<f4"), ("k", "<i2"), ("ny", "<f4"), ("nz", "<f8")])
+    b = rng.normal(0, 50, (m, 6))
+    for j, name in enumerate(("x", "y", "z", "nx", "ny", "nz")):
+        rec[name] = b[:, j]
+    rec["red"] = 200; rec["k"] = -3
+    bhead = ("ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty double x\nproperty uchar red\nproperty float y\n"
+             "property float z\nproperty float nx\nproperty short k\nproperty float ny\nproperty double nz\nelement face 0\n"
+             "property list uchar int vertex_indices\nend_header\n" % m).encode()
+    (tmp_path / "mixed.ply").write_bytes(bhead + rec.tobytes() + b"tail")
+    got = pcd.ply_read(str(tmp_path / "mixed.ply"))
+    wantb = np.zeros((m, 8), np.float32)
+    for j, name in zip((0, 1, 2, 4, 5, 6), ("x", "y", "z", "nx", "ny", "nz")):
+        wantb[:, j] = rec[name].astype(np.float32)
+    assert np.array_equal(got, wantb)
+    (tmp_path / "cut.ply").write_bytes(bhead + rec.tobytes()[:-5])
+    with pytest.raises(pcd.PcdError, match="truncated"):
+        pcd.ply_read(str(tmp_path / "cut.ply"))
+
+
 # ------------------------------------------------------------------ oracle: loader / NN -----
 def test_direction_trans(orc):
     a = np.zeros((4, 8), np.float32)
