@@ -164,7 +164,7 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
                        (f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J "
                         f"{'fp64 blocks (32 B/query)' if args.exchange_wire == 'f64' else 'blocks rounded to float4 by k_pack_blocks_f32 (16 B/query; fp64 results stay on the producer)'} + "
                         "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass") if args.exchange != "p2p" else
-                       ("per pass: r and J fp64 blocks (32 B/query) pushed into every peer's symmetric-memory buffer by copy engines over "
+                       (f"per pass: r and J {'fp64 blocks (32 B/query)' if args.exchange_wire == 'f64' else 'blocks rounded to float4 (16 B/query)'} pushed into every peer's symmetric-memory buffer by copy engines over "
                         "NVLink + signal barrier + all_reduce of sum r^2, on side streams overlapping the next pass")}}
 
 
@@ -344,11 +344,11 @@ def run_b200(args):
     shard = load_shard()
     gather = None
     if world > 1:
+        def pack(r_, J_, out, st):
+            ctx.pack_blocks_f32_dev(r_.data_ptr(), J_.data_ptr(), Q, out.data_ptr(), st)
         if args.exchange == "p2p":
-            gather = shard.PeerExchange(Q, dev)
+            gather = shard.PeerExchange(Q, dev, wire=args.exchange_wire, pack=pack if args.exchange_wire == "f32" else None)
         else:
-            def pack(r_, J_, out, st):
-                ctx.pack_blocks_f32_dev(r_.data_ptr(), J_.data_ptr(), Q, out.data_ptr(), st)
             gather = shard.Exchange(Q, dev, root=0 if args.exchange == "gather" else None, wire=args.exchange_wire,
                                     pack=pack if args.exchange_wire == "f32" else None)
     step_no = [0]
@@ -416,7 +416,7 @@ def run_b200(args):
         r_all, J_all, _ = gather.wait()
         torch.cuda.synchronize()
         lb = (step_no[0] - 1) & 1
-        wire_t = torch.float32 if (args.exchange_wire == "f32" and args.exchange != "p2p") else torch.float64
+        wire_t = torch.float32 if args.exchange_wire == "f32" else torch.float64
         sent_r, sent_J = d_rb[lb].to(wire_t), d_Jb[lb].to(wire_t)          # what this rank put on the wire
         chk = torch.stack([sent_r.double().nan_to_num().sum(), sent_J.double().nan_to_num().sum()])
         dist.all_reduce(chk, op=dist.ReduceOp.SUM)

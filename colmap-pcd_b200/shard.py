@@ -122,10 +122,15 @@ class PeerExchange:
     from the search kernels that run the next pass at the same time -- then joins a signal-pad barrier, after which
     every rank holds every block.  Two receive buffers alternate, so a consumer has a whole pass to read one.
     The fp64 statistics still go through a (tiny) NCCL all-reduce.
+    wire = "f32": the blocks are first rounded to float4 {r, J0, J1, J2} by `pack` (see Exchange) and one 16 B/query
+    copy per peer replaces the two fp64 ones.
     """
 
-    def __init__(self, q_per_rank, device, group=None):
+    def __init__(self, q_per_rank, device, group=None, wire="f64", pack=None):
         import torch.distributed._symmetric_memory as symm
+        if wire not in ("f64", "f32") or (wire == "f32" and pack is None):
+            raise ValueError("PeerExchange: wire is 'f64' or 'f32' (the latter needs the pack callable)")
+        self.wire, self.pack = wire, pack
         self.group = group if group is not None else dist.group.WORLD
         self.world = dist.get_world_size(self.group)
         self.rank = dist.get_rank(self.group)
@@ -133,11 +138,15 @@ class PeerExchange:
         dev = torch.device(device)
         n = self.world * self.q
         self.recv, self.hdl, self.peer_views = [], [], []
+        wdt = torch.float32 if wire == "f32" else torch.float64
         for _ in range(2):
-            t = symm.empty(4 * n, dtype=torch.float64, device=dev)
+            t = symm.empty(4 * n, dtype=wdt, device=dev)
             h = symm.rendezvous(t, group=self.group)
             self.recv.append(t); self.hdl.append(h)
-            self.peer_views.append([h.get_buffer(p, (4 * n,), torch.float64) for p in range(self.world)])
+            self.peer_views.append([h.get_buffer(p, (4 * n,), wdt) for p in range(self.world)])
+        if wire == "f32":
+            self.w_local = [torch.empty((self.q, 4), dtype=torch.float32, device=dev) for _ in range(2)]
+            self.pack_stream = torch.cuda.Stream(device=dev, priority=-1)
         self.stats = torch.zeros(3, dtype=torch.float64, device=dev)
         self.main = torch.cuda.Stream(device=dev, priority=-1)
         self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(self.world)]
@@ -147,20 +156,32 @@ class PeerExchange:
 
     def views(self, buf):
         n = self.world * self.q
+        if self.wire == "f32":
+            w = self.recv[buf].view(n, 4)
+            return w[:, 0], w[:, 1:4]
         return self.recv[buf][:n], self.recv[buf][n:].view(n, 3)
 
     def start(self, r, J, stats, buf=0):
         n, q, me = self.world * self.q, self.q, self.rank
         cur = torch.cuda.current_stream()
+        src = cur
+        if self.wire == "f32":
+            self.pack_stream.wait_stream(cur)
+            with torch.cuda.stream(self.pack_stream):
+                self.pack(r, J, self.w_local[buf], self.pack_stream.cuda_stream)
+            src, wf = self.pack_stream, self.w_local[buf].reshape(-1)
         Jf = J.reshape(-1)
         for k in range(self.world):                      # own slot first, then the peers in ring order
             p = (me + k) % self.world
             st = self.streams[p]
-            st.wait_stream(cur)
+            st.wait_stream(src)
             with torch.cuda.stream(st):
                 dst = self.peer_views[buf][p]
-                dst[me * q:(me + 1) * q].copy_(r, non_blocking=True)
-                dst[n + 3 * me * q:n + 3 * (me + 1) * q].copy_(Jf, non_blocking=True)
+                if self.wire == "f32":
+                    dst[4 * me * q:4 * (me + 1) * q].copy_(wf, non_blocking=True)
+                else:
+                    dst[me * q:(me + 1) * q].copy_(r, non_blocking=True)
+                    dst[n + 3 * me * q:n + 3 * (me + 1) * q].copy_(Jf, non_blocking=True)
         self.main.wait_stream(cur)
         for st in self.streams:
             self.main.wait_stream(st)
