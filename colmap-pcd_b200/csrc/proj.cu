@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 
 namespace pcd {
 
@@ -221,6 +222,90 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
   }
 }
 
+// Experimental variant of the feature-mask path (selected by PCD_B200_PROJ_COOP=<pixels>, default off; A/B tool:
+// tools/explore_proj.py).  Points near the camera have splats of tens of thousands of pixels, and the lane that owns
+// one walks all its mask words alone while 31 lanes wait.  Here a splat larger than `coop_px` pixels is handed to the
+// whole warp: the (row group, mask word) tiles of its rectangle are dealt round-robin to the lanes.  Winners are
+// unchanged (atomicMin commutes).
+__device__ __forceinline__ void mask_tile(const uint32_t* __restrict__ mask, const uint32_t* __restrict__ summ,
+                                          unsigned long long* __restrict__ zbuf, const ImgParams& P, int vg, int wd, int ua,
+                                          int ub, int va, int vb, unsigned long long packed) {
+  uint32_t any = __ldg(&summ[(int64_t)vg * P.words + wd]);
+  if (!any) return;
+  const int lo = max(ua - (wd << 5), 0), hi = min(ub - (wd << 5), 31);
+  const uint32_t m = (hi == 31 ? 0xffffffffu : ((1u << (hi + 1)) - 1u)) & ~((1u << lo) - 1u);
+  if (!(any & m)) return;
+  const int v1 = min(vb, (vg << MASK_ROWS_LOG2) + MASK_ROWS - 1);
+  for (int v = max(va, vg << MASK_ROWS_LOG2); v <= v1; v++) {
+    uint32_t bits = __ldg(&mask[(int64_t)v * P.words + wd]) & m;
+    while (bits) {
+      const int bpos = __ffs(bits) - 1; bits &= bits - 1;
+      unsigned long long* px = zbuf + (int64_t)v * P.w + (wd << 5) + bpos;
+      if (packed < *px) atomicMin(px, packed);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) k_project_coop(SubmapView sm, ImgParams P, const uint32_t* __restrict__ mask,
+                                                      const uint32_t* __restrict__ summ, unsigned long long* __restrict__ zbuf,
+                                                      unsigned long long* __restrict__ stats, int coop_px) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  unsigned long long n_pts = 0, n_px = 0, n_cells = 0;
+  for (int64_t s = warp; s < sm.n_seg; s += nwarps) {
+    const uint2 sg = __ldg(&sm.seg[s]);
+    const int64_t c = sg.x;
+    float x = (float)sm.keys[3 * c] * sm.len, y = (float)sm.keys[3 * c + 1] * sm.height, z = (float)sm.keys[3 * c + 2] * sm.width;
+    bool in = true;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+      float v = P.planes[4 * k] * x + P.planes[4 * k + 1] * y;
+      v = v + P.planes[4 * k + 2] * z;
+      v = v + P.planes[4 * k + 3];
+      in = in && (v <= 0.0f);
+    }
+    if (!in) continue;
+    const uint32_t b = sg.y, e = min(b + sm.seg_len, sm.start[c + 1]);
+    if (lane == 0 && b == sm.start[c]) n_cells++;
+    for (uint32_t j0 = b; j0 < e; j0 += 32) {
+      const uint32_t j = j0 + lane;
+      unsigned long long packed = 0;
+      int ua = 0, ub = -1, va = 0, vb = -1;
+      const bool rect = j < e && point_rect(P, __ldg(&sm.pts[j]), packed, ua, ub, va, vb, n_pts, n_px);
+      const bool big = rect && (int64_t)(ub - ua + 1) * (vb - va + 1) > coop_px;
+      if (rect && !big) {
+        for (int vg = va >> MASK_ROWS_LOG2; vg <= (vb >> MASK_ROWS_LOG2); vg++)
+          for (int wd = ua >> 5; wd <= (ub >> 5); wd++) mask_tile(mask, summ, zbuf, P, vg, wd, ua, ub, va, vb, packed);
+      }
+      unsigned todo = __ballot_sync(0xffffffffu, big);
+      while (todo) {
+        const int src = __ffs(todo) - 1; todo &= todo - 1;
+        const unsigned long long pk = __shfl_sync(0xffffffffu, packed, src);
+        const int a0 = __shfl_sync(0xffffffffu, ua, src), a1 = __shfl_sync(0xffffffffu, ub, src);
+        const int r0 = __shfl_sync(0xffffffffu, va, src), r1 = __shfl_sync(0xffffffffu, vb, src);
+        const int w0 = a0 >> 5, nW = (a1 >> 5) - w0 + 1, g0 = r0 >> MASK_ROWS_LOG2;
+        const int tot = nW * ((r1 >> MASK_ROWS_LOG2) - g0 + 1);
+        for (int t = lane; t < tot; t += 32) {
+          const int gi = t / nW;
+          mask_tile(mask, summ, zbuf, P, g0 + gi, w0 + (t - gi * nW), a0, a1, r0, r1, pk);
+        }
+      }
+    }
+  }
+  if (stats) {
+    for (int o = 16; o > 0; o >>= 1) {
+      n_pts += __shfl_down_sync(0xffffffffu, n_pts, o);
+      n_px += __shfl_down_sync(0xffffffffu, n_px, o);
+    }
+    if (lane == 0) {
+      if (n_cells) atomicAdd(&stats[0], n_cells);
+      if (n_pts) atomicAdd(&stats[1], n_pts);
+      if (n_px) atomicAdd(&stats[2], n_px);
+    }
+  }
+}
+
 __global__ void k_gather_winners(const int64_t* __restrict__ px, int64_t n, const unsigned long long* __restrict__ zbuf,
                                  int32_t* __restrict__ widx, float* __restrict__ wrange, unsigned long long* __restrict__ stats) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -288,7 +373,10 @@ static int project_one(pcd_cloud* c, const pcd_image* img, const double coef[4],
     int blocks = (int)((warps + 7) / 8);
     int cap = ctx->sm_count * 16; if (blocks > cap) blocks = cap;
     ProfScope ps(ctx, PCD_K_PROJECT, st);
+    int coop_px = 0;                                          // experimental variant, off unless asked for
+    if (!dense) { if (const char* e = getenv("PCD_B200_PROJ_COOP")) coop_px = atoi(e); }
     if (dense) k_project<true><<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats);
+    else if (coop_px > 0) k_project_coop<<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats, coop_px);
     else k_project<false><<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats);
     PCD_LAUNCH_CHECK(ctx);
   }
