@@ -68,4 +68,5 @@ for env in envs:
                       ref = res
                   same = bool(np.array_equal(ref, res))
                   print(f"cell {cell:7.4f} xs {xs:2d} cells {info['n_cells']:>11d} K1 {g:2d}: search {ms / n:8.3f} ms  "
-                        f"(far {fs / n:6.3f}) keysort {ks / n:6.3f} ms  {Q / (ms / n) / 1e3:8.1f} Mq/s  hits {(res >= 0).mean():.3f} same={same}", flush=True)
+                        f"far {fs / n:6.3f} keysort {ks / n:6.3f} ms  total {(ms + fs + ks) / n:7.3f} ms  "
+                        f"{Q / ((ms + fs) / n) / 1e3:8.1f} Mq/s (search+far)  hits {(res >= 0).mean():.3f} same={same}", flush=True)
