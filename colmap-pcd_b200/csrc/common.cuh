@@ -89,7 +89,6 @@ struct pcd_ctx {
   pcd::DevBuf stage_in[2], stage_out[2], stage_aux[2];
   pcd::PinBuf pin_in[2], pin_out[2];
   pcd::DevBuf img_buf, feat_buf, zbuf, sel_buf, far_q, qrec, eval_partial;
-  pcd::DevBuf tile_cnt, tile_start, tile_jobs, srec, sid;     // tile-staged search (nn_tile.cu)
   // optional per-kernel CUDA-event timing (pcd_ctx_profile); spans are resolved lazily
   bool prof = false;
   struct Span { cudaEvent_t a, b; int which; };

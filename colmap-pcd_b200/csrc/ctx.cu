@@ -42,8 +42,7 @@ void pcd_ctx_destroy(pcd_ctx* c) {
   cudaDeviceSynchronize();
   pcd::DevBuf* bufs[] = {&c->keys, &c->keys_alt, &c->vals, &c->vals_alt, &c->cub_tmp, &c->misc, &c->partial,
                          &c->stage_in[0], &c->stage_in[1], &c->stage_out[0], &c->stage_out[1],
-                         &c->stage_aux[0], &c->stage_aux[1], &c->img_buf, &c->feat_buf, &c->zbuf, &c->sel_buf, &c->far_q, &c->qrec, &c->eval_partial,
-                         &c->tile_cnt, &c->tile_start, &c->tile_jobs, &c->srec, &c->sid};
+                         &c->stage_aux[0], &c->stage_aux[1], &c->img_buf, &c->feat_buf, &c->zbuf, &c->sel_buf, &c->far_q, &c->qrec, &c->eval_partial};
   for (auto* b : bufs) b->release();
   for (int i = 0; i < 2; i++) { c->pin_in[i].release(); c->pin_out[i].release(); }
   for (int i = 0; i < 8; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);

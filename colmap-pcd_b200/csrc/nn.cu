@@ -27,22 +27,45 @@
 namespace cg = cooperative_groups;
 #include <math.h>
 #include <stdlib.h>
-#include "nn_dev.cuh"
 
 namespace pcd {
 
-// Written in original order with coalesced stores; the search gathers the record through the sorted order, one
-// aligned 16-byte load per query instead of three doubles plus the radius source.
+struct RadiusSrc {
+  const double* radius;      // per query or NULL
+  const int32_t* opt_num;    // per query GlobalOptNum or NULL
+  double max_r, min_r, drop;
+  double fixed;              // used when both are NULL (INFINITY = unbounded)
+};
+
+__device__ __forceinline__ double query_radius(const RadiusSrc& rs, uint32_t i) {
+  if (rs.radius) return rs.radius[i];
+  if (rs.opt_num) return sweep_range(rs.opt_num[i], rs.max_r, rs.min_r, rs.drop);
+  return rs.fixed;
+}
+
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
+
+// Query record used by the search kernels: the float-cast query (the reference's cast, ply.cc:92) and the
+// search radius rounded UP to float (INFINITY = unbounded, NaN = invalid radius).  Written in original
+// order with coalesced stores; the search gathers it through the sorted order, one aligned 16-byte
+// load per query instead of three doubles plus the radius source.
 __global__ void k_query_keys(const double* __restrict__ q, RadiusSrc rs, int64_t n, GridView g, uint32_t* __restrict__ keys,
                              uint32_t* __restrict__ vals, float4* __restrict__ qrec) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const float4 r = query_record(q, rs, i);
-  qrec[i] = r;
+  float x = (float)q[3 * i], y = (float)q[3 * i + 1], z = (float)q[3 * i + 2];
+  const double R = query_radius(rs, (uint32_t)i);
+  float Rf = INFINITY;
+  // The float ball must hold every point the reference's fp64 test |l - p| <= R can accept: the cast above moves the
+  // query by at most |x| 2^-24 per axis, so the radius grows by the sum of the three before it is rounded up.
+  if (R != INFINITY)
+    Rf = (R < 0.0 || isnan(R)) ? __int_as_float(0x7fc00000)
+                               : __double2float_ru(R + (fabs(q[3 * i]) + fabs(q[3 * i + 1]) + fabs(q[3 * i + 2])) * 5.9604644775390625e-8);
+  qrec[i] = make_float4(x, y, z, Rf);
   if (keys) {
-    int cx = clampi((int)floorf((r.x - g.ox) * g.inv_cx), 0, g.dx - 1);
-    int cy = clampi((int)floorf((r.y - g.oy) * g.inv_c), 0, g.dy - 1);
-    int cz = clampi((int)floorf((r.z - g.oz) * g.inv_c), 0, g.dz - 1);
+    int cx = clampi((int)floorf((x - g.ox) * g.inv_cx), 0, g.dx - 1);
+    int cy = clampi((int)floorf((y - g.oy) * g.inv_c), 0, g.dy - 1);
+    int cz = clampi((int)floorf((z - g.oz) * g.inv_c), 0, g.dz - 1);
     keys[i] = (uint32_t)(((int64_t)cz * g.dy + cy) * g.dx + cx);
     vals[i] = (uint32_t)i;
   }
@@ -61,6 +84,144 @@ constexpr int NN_THREADS = 256;
 #ifndef FAR_GROUP
 #define FAR_GROUP 16      // lanes per far query (32, 16 or 8)
 #endif
+constexpr float SHRINK = 0.999999f;   // applied to lower bounds before comparing with a float d2
+constexpr float GROW = 1.000001f;
+
+// Per-query search state.  All geometry is in metres relative to the grid origin.
+struct Query {
+  float qx, qy, qz;          // float-cast query (the reference's cast, ply.cc:92)
+  float px, py, pz;          // q - origin
+  int ix, iy, iz;            // own cell (clamped into the grid)
+  float R2;                  // conservative float bound on radius^2 (INFINITY when unbounded)
+  float rw;                  // the record's radius word (float radius rounded up, INFINITY, or NaN = invalid)
+  unsigned long long best;   // (float bits of d2 << 32) | original index
+
+  __device__ __forceinline__ float best_d2() const { return __uint_as_float((unsigned)(best >> 32)); }
+  __device__ __forceinline__ float bound2() const { return fminf(best_d2(), R2); }
+
+  __device__ __forceinline__ void scan(const GridView& g, uint32_t b, uint32_t e, int first, int stride) {
+    unsigned long long bst = best;
+    for (uint32_t j = b + first; j < e; j += stride) {
+      float4 p = __ldg(&g.pts[j]);
+      float ddx = qx - p.x, ddy = qy - p.y, ddz = qz - p.z;
+      float d = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
+      unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | __float_as_uint(p.w);
+      bst = key < bst ? key : bst;
+    }
+    best = bst;
+  }
+
+  // lower bound (metres) on the distance along one axis from coordinate p to cells [lo, hi] of edge c
+  static __device__ __forceinline__ float gap(float p, int lo, int hi, float c, float margin) {
+    float a = fmaxf((float)lo * c - p, p - (float)(hi + 1) * c);
+    return fmaxf(a - margin, 0.0f);
+  }
+
+  // x interval [x0, x1] (cells of edge cx) clipped to the chord of the ball of squared radius b2 at
+  // squared (y, z) offset g2, and to the grid
+  __device__ __forceinline__ bool chord(const GridView& g, float b2, float g2, int& x0, int& x1) const {
+    float hx = sqrtf(b2 - g2) * GROW + g.margin;          // INFINITY stays INFINITY
+    x0 = max(max(x0, 0), (int)floorf((px - hx) * g.inv_cx));
+    x1 = min(min(x1, g.dx - 1), (int)floorf((px + hx) * g.inv_cx));
+    return x0 <= x1;
+  }
+
+  // squared radius (metres^2) within which the block x: +-kx cells, y/z: +-k cells around the own
+  // cell is known to hold every cloud point; INFINITY when the block covers the grid
+  __device__ __forceinline__ float certified2(const GridView& g, int kx, int k) const {
+    float rc = INFINITY;
+    if (ix - kx > 0) rc = fminf(rc, px - (float)(ix - kx) * g.cx);
+    if (ix + kx < g.dx - 1) rc = fminf(rc, (float)(ix + kx + 1) * g.cx - px);
+    if (iy - k > 0) rc = fminf(rc, py - (float)(iy - k) * g.c);
+    if (iy + k < g.dy - 1) rc = fminf(rc, (float)(iy + k + 1) * g.c - py);
+    if (iz - k > 0) rc = fminf(rc, pz - (float)(iz - k) * g.c);
+    if (iz + k < g.dz - 1) rc = fminf(rc, (float)(iz + k + 1) * g.c - pz);
+    if (rc == INFINITY) return INFINITY;
+    rc = fmaxf(rc - g.margin, 0.0f);
+    return rc * rc * SHRINK;
+  }
+
+  // loads the record of query `i`, derives its cell, radius bound and validity
+  __device__ __forceinline__ bool load(const GridView& g, const float4* __restrict__ qrec, uint32_t i) {
+    return from_record(g, __ldg(&qrec[i]));
+  }
+  __device__ __forceinline__ float4 record() const { return make_float4(qx, qy, qz, rw); }
+  __device__ __forceinline__ bool from_record(const GridView& g, const float4 r) {
+    qx = r.x; qy = r.y; qz = r.z; rw = r.w;
+    px = qx - g.ox; py = qy - g.oy; pz = qz - g.oz;
+    ix = clampi((int)floorf(px * g.inv_cx), 0, g.dx - 1);
+    iy = clampi((int)floorf(py * g.inv_c), 0, g.dy - 1);
+    iz = clampi((int)floorf(pz * g.inv_c), 0, g.dz - 1);
+    R2 = r.w == INFINITY ? INFINITY : __fmul_ru(r.w, r.w) * 1.00001f + 1e-12f;     // conservative bound on radius^2
+    bool valid = isfinite(qx) && isfinite(qy) && isfinite(qz) && !isnan(r.w) && g.n > 0;
+    if (valid && R2 != INFINITY) {
+      // no cloud point can be within R of a query farther than R from the grid box
+      float bx = gap(px, 0, g.dx - 1, g.cx, g.margin), by = gap(py, 0, g.dy - 1, g.c, g.margin),
+            bz = gap(pz, 0, g.dz - 1, g.c, g.margin);
+      if ((bx * bx + by * by + bz * bz) * SHRINK > R2) valid = false;
+    }
+    best = ~0ull;
+    return valid;
+  }
+
+  // One row (iy + DY, iz + DZ) of phase 1.  gy2 / gz2: squared axis gaps, NaN for rows outside the grid.
+  __device__ __forceinline__ void row(const GridView& g, int kx, int dy, int dz, float gy2, float gz2) {
+    const float g2 = (gy2 + gz2) * SHRINK;
+    const float b2 = bound2();
+    if (!(g2 <= b2)) return;                               // pruned, or outside the grid (NaN)
+    int x0 = ix - kx, x1 = ix + kx;
+    if (!chord(g, b2, g2, x0, x1)) return;
+    const uint32_t lin = ((uint32_t)(iz + dz) * (uint32_t)g.dy + (uint32_t)(iy + dy)) * (uint32_t)g.dx;
+    const uint32_t b = __ldg(&g.cell_start[lin + x0]);
+    const uint32_t e = __ldg(&g.cell_start[lin + x1 + 1]);
+    scan(g, b, e, 0, 1);
+  }
+
+  // phase 1: own cell, rest of the centre row, then rings 1..K1 of rows; returns true when certified
+  template <int K1>
+  __device__ __forceinline__ bool search_block(const GridView& g) {
+    const int kx = K1 * g.xs;
+    // squared axis gaps to the rows / slabs at offset -K1..K1 (NaN outside the grid -> never scanned)
+    float gy2[2 * K1 + 1], gz2[2 * K1 + 1];
+#pragma unroll
+    for (int d = -K1; d <= K1; d++) {
+      float a = gap(py, iy + d, iy + d, g.c, g.margin), b = gap(pz, iz + d, iz + d, g.c, g.margin);
+      gy2[d + K1] = (iy + d < 0 || iy + d >= g.dy) ? __int_as_float(0x7fc00000) : a * a;
+      gz2[d + K1] = (iz + d < 0 || iz + d >= g.dz) ? __int_as_float(0x7fc00000) : b * b;
+    }
+    // own cell, then the rest of the centre row inside the chord of the bound it gave
+    const uint32_t lin0 = ((uint32_t)iz * (uint32_t)g.dy + (uint32_t)iy) * (uint32_t)g.dx;
+    const uint32_t b0 = __ldg(&g.cell_start[lin0 + ix]), e0 = __ldg(&g.cell_start[lin0 + ix + 1]);
+    scan(g, b0, e0, 0, 1);
+    {
+      int x0 = ix - kx, x1 = ix + kx;
+      chord(g, bound2(), 0.0f, x0, x1);                    // always contains the own cell
+      x0 = min(x0, ix); x1 = max(x1, ix);
+      const uint32_t b = __ldg(&g.cell_start[lin0 + x0]), e = __ldg(&g.cell_start[lin0 + x1 + 1]);
+      scan(g, b, b0, 0, 1);
+      scan(g, e0, e, 0, 1);
+    }
+#pragma unroll
+    for (int k = 1; k <= K1; k++) {
+      // ring k of rows, nearest first: the four axis rows, then the rest of the ring
+#pragma unroll
+      for (int t = 0; t <= k; t++) {
+        // offsets (+-k, +-t) and (+-t, +-k); t = 0 gives the axis rows, t = k the corners
+#pragma unroll
+        for (int s = 0; s < 8; s++) {
+          const int a = (s & 1) ? k : -k, bsgn = (s & 2) ? t : -t;
+          const int dy = (s & 4) ? a : bsgn, dz = (s & 4) ? bsgn : a;
+          if (t == 0 && (s & 2)) continue;                 // +-0 duplicates
+          if (t == k && (s & 4)) continue;                 // corners appear in both orientations
+          row(g, kx, dy, dz, gy2[dy + K1], gz2[dz + K1]);
+        }
+      }
+      const float rc2 = certified2(g, kx, k);
+      if (best_d2() <= rc2 || R2 <= rc2) return true;
+    }
+    return false;
+  }
+};
 
 // ---- phase 2: far queries, one GROUP of FAR_GROUP lanes per query, best-first over the block occupancy words ----
 // Every lane of a group holds the same query; the blocks of a Chebyshev shell are spread over the lanes (one
@@ -238,152 +399,19 @@ struct FarSearch {
   }
 };
 
-// ---- far queries, second form: ONE THREAD per queued query over the occupancy words ----
-// Blocks (4 x 4 x 4 cubic cells) are visited in Chebyshev shells around the query's block.  A block is bounded per axis
-// first (three gaps); its occupancy word is fetched only when the box can still matter, then masked by the cells whose
-// per-axis gaps are inside the bound (a 64-bit AND with three table masks) and the surviving cells are tested against
-// the ball one by one; a cell's points are the x run of its (y, z) row between two cell_start entries, clipped to the
-// chord.  Cells of the 3 x 3 x (+-xs) window that phase 1 has already examined are skipped (`seen`).  The lower
-// bounds are the ones of FarSearch above (cell geometry minus the float margin), so the exactness argument is the same.
-__constant__ unsigned long long FAR_TX[16], FAR_TY[16], FAR_TZ[16];     // bit (z * 4 + y) * 4 + x set iff x (y, z) is in the 4-bit axis mask
-
-__device__ __forceinline__ float sel4(float a0, float a1, float a2, float a3, int l) {
-  return l == 0 ? a0 : (l == 1 ? a1 : (l == 2 ? a2 : a3));
-}
-
-struct Far2 {
-  const GridView& g;
-  Query& Q;
-  float b2;
-  const bool seen;           // phase 1 has examined rows iy-1..iy+1, iz-1..iz+1 over x cells [ix - xs, ix + xs]
-
-  __device__ __forceinline__ void run_x(int cy, int cz, int x0, int x1) {
-    if (x0 > x1) return;
-    const uint32_t lin = ((uint32_t)cz * (uint32_t)g.dy + (uint32_t)cy) * (uint32_t)g.dx;
-    const uint32_t b = __ldg(&g.cell_start[lin + x0]), e = __ldg(&g.cell_start[lin + x1 + 1]);
-    if (b == e) return;
-    Q.scan(g, b, e, 0, 1);
-    b2 = Q.bound2();
+// The search reports the nearest point inside the conservative float ball.  The reference's accept test
+// |l - p| <= range in fp64 (src/optim/bundle_adjustment.cc:398-400, Eigen's (a - b).norm() = sqrt(x2 + (y2 + z2)))
+// is applied afterwards in ORIGINAL query order, where p, the radius and idx stream in coalesced: by
+// k_assoc_record on the association path, by k_nn_radius_filter for pcd_nn_batch with a radius.
+__device__ __forceinline__ void nn_write(unsigned long long best, uint32_t i, int32_t* __restrict__ idx_out,
+                                         float* __restrict__ d2_out) {
+  int32_t idx = -1; float d2 = INFINITY;
+  if (best != ~0ull) {
+    idx = (int32_t)(uint32_t)(best & 0xffffffffu);
+    d2 = __uint_as_float((unsigned)(best >> 32));
   }
-
-  __device__ __forceinline__ void block(int X, int Y, int Z) {
-    const int sx = 4 * g.xs;
-    {
-      const float a = Query::gap(Q.px, X * sx, X * sx + sx - 1, g.cx, g.margin), b = Query::gap(Q.py, 4 * Y, 4 * Y + 3, g.c, g.margin),
-                  c = Query::gap(Q.pz, 4 * Z, 4 * Z + 3, g.c, g.margin);
-      if (!((a * a + (b * b + c * c)) * SHRINK <= b2)) return;
-    }
-    unsigned long long w = __ldg(&g.occ[((int64_t)Z * g.nby + Y) * g.nbx + X]);
-    if (!w) return;
-    float gx2[4], gy2[4], gz2[4];
-    unsigned mx = 0, my = 0, mz = 0;
-#pragma unroll
-    for (int l = 0; l < 4; l++) {
-      const int cxc = 4 * X + l;
-      const float a = Query::gap(Q.px, cxc * g.xs, cxc * g.xs + g.xs - 1, g.cx, g.margin), b = Query::gap(Q.py, 4 * Y + l, 4 * Y + l, g.c, g.margin),
-                  c = Query::gap(Q.pz, 4 * Z + l, 4 * Z + l, g.c, g.margin);
-      gx2[l] = a * a; gy2[l] = b * b; gz2[l] = c * c;
-      if (gx2[l] * SHRINK <= b2) mx |= 1u << l;
-      if (gy2[l] * SHRINK <= b2) my |= 1u << l;
-      if (gz2[l] * SHRINK <= b2) mz |= 1u << l;
-    }
-    w &= FAR_TX[mx] & FAR_TY[my] & FAR_TZ[mz];
-    while (w) {
-      const int bit = __ffsll((long long)w) - 1;
-      w &= w - 1;
-      const int lx = bit & 3, ly = (bit >> 2) & 3, lz = bit >> 4;
-      const float yz2 = sel4(gy2[0], gy2[1], gy2[2], gy2[3], ly) + sel4(gz2[0], gz2[1], gz2[2], gz2[3], lz);
-      if (!((sel4(gx2[0], gx2[1], gx2[2], gx2[3], lx) + yz2) * SHRINK <= b2)) continue;
-      const int cy = 4 * Y + ly, cz = 4 * Z + lz;
-      int x0 = (4 * X + lx) * g.xs, x1 = x0 + g.xs - 1;
-      if (!Q.chord(g, b2, yz2 * SHRINK, x0, x1)) continue;
-      if (seen && abs(cy - Q.iy) <= 1 && abs(cz - Q.iz) <= 1) {
-        run_x(cy, cz, x0, min(x1, Q.ix - g.xs - 1));
-        run_x(cy, cz, max(x0, Q.ix + g.xs + 1), x1);
-      } else run_x(cy, cz, x0, x1);
-    }
-  }
-
-  __device__ __forceinline__ float certified2(int bx, int by, int bz, int kb) const {
-    const int sx = 4 * g.xs;
-    float rc = INFINITY;
-    const int x0 = (bx - kb) * sx, x1 = (bx + kb + 1) * sx - 1, y0 = 4 * (by - kb), y1 = 4 * (by + kb) + 3, z0 = 4 * (bz - kb), z1 = 4 * (bz + kb) + 3;
-    if (x0 > 0) rc = fminf(rc, Q.px - (float)x0 * g.cx);
-    if (x1 < g.dx - 1) rc = fminf(rc, (float)(x1 + 1) * g.cx - Q.px);
-    if (y0 > 0) rc = fminf(rc, Q.py - (float)y0 * g.c);
-    if (y1 < g.dy - 1) rc = fminf(rc, (float)(y1 + 1) * g.c - Q.py);
-    if (z0 > 0) rc = fminf(rc, Q.pz - (float)z0 * g.c);
-    if (z1 < g.dz - 1) rc = fminf(rc, (float)(z1 + 1) * g.c - Q.pz);
-    if (rc == INFINITY) return INFINITY;
-    rc = fmaxf(rc - g.margin, 0.0f);
-    return rc * rc * SHRINK;
-  }
-
-  __device__ __forceinline__ void run() {
-    const int bx = (Q.ix / g.xs) >> 2, by = Q.iy >> 2, bz = Q.iz >> 2;
-    block(bx, by, bz);
-    const int kmax = max(g.nbx, max(g.nby, g.nbz));
-    for (int kb = 1; kb <= kmax; kb++) {
-      {
-        const float rc2 = certified2(bx, by, bz, kb - 1);
-        if (rc2 == INFINITY || b2 <= rc2) return;
-      }
-      const int Z0 = max(bz - kb, 0), Z1 = min(bz + kb, g.nbz - 1), Y0 = max(by - kb, 0), Y1 = min(by + kb, g.nby - 1);
-      for (int Z = Z0; Z <= Z1; Z++)
-        for (int Y = Y0; Y <= Y1; Y++) {
-          const bool face = abs(Z - bz) == kb || abs(Y - by) == kb;
-          if (face) {
-            for (int X = max(bx - kb, 0); X <= min(bx + kb, g.nbx - 1); X++) block(X, Y, Z);
-          } else {
-            if (bx - kb >= 0) block(bx - kb, Y, Z);
-            if (bx + kb < g.nbx) block(bx + kb, Y, Z);
-          }
-        }
-    }
-  }
-};
-
-__global__ void __launch_bounds__(NN_THREADS, 4) k_nn_far2(GridView g, int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
-                                                        const FarItem* __restrict__ far, const unsigned int* __restrict__ far_count,
-                                                        unsigned int* __restrict__ next) {
-  const unsigned count = *far_count;
-  const int lane = threadIdx.x & 31;
-  const uint4* fq = reinterpret_cast<const uint4*>(far);
-  for (;;) {
-    unsigned e0 = 0;
-    if (lane == 0) e0 = atomicAdd(next, 32u);
-    e0 = __shfl_sync(0xffffffffu, e0, 0);
-    if (e0 >= count) return;
-    const unsigned e = e0 + (unsigned)lane;
-    if (e < count) {
-      const uint4 c0 = __ldg(&fq[2 * (size_t)e]), c1 = __ldg(&fq[2 * (size_t)e + 1]);
-      Query Q;
-      const bool valid = Q.from_record(g, make_float4(__uint_as_float(c1.x), __uint_as_float(c1.y), __uint_as_float(c1.z), __uint_as_float(c1.w)));
-      Q.best = ((unsigned long long)c0.y << 32) | c0.x;
-      if (valid) {
-        Far2 F{g, Q, Q.bound2(), c0.w != 0u};
-        F.run();
-      }
-      nn_write(Q.best, c0.z, idx_out, d2_out);
-    }
-    __syncwarp();
-  }
-}
-
-static void far2_tables_init(int device) {          // __constant__ tables are per device
-  static bool done[64] = {};
-  if (device >= 0 && device < 64 && done[device]) return;
-  unsigned long long tx[16], ty[16], tz[16];
-  for (int m = 0; m < 16; m++) {
-    tx[m] = ty[m] = tz[m] = 0;
-    for (int bit = 0; bit < 64; bit++) {
-      if ((m >> (bit & 3)) & 1) tx[m] |= 1ull << bit;
-      if ((m >> ((bit >> 2) & 3)) & 1) ty[m] |= 1ull << bit;
-      if ((m >> (bit >> 4)) & 1) tz[m] |= 1ull << bit;
-    }
-  }
-  cudaMemcpyToSymbol(FAR_TX, tx, sizeof tx); cudaMemcpyToSymbol(FAR_TY, ty, sizeof ty); cudaMemcpyToSymbol(FAR_TZ, tz, sizeof tz);
-  if (device >= 0 && device < 64) done[device] = true;
+  idx_out[i] = idx;
+  if (d2_out) d2_out[i] = d2;
 }
 
 __global__ void k_nn_radius_filter(const double* __restrict__ q, RadiusSrc rs, int64_t n, const float4* __restrict__ aos,
@@ -399,6 +427,11 @@ __global__ void k_nn_radius_filter(const double* __restrict__ q, RadiusSrc rs, i
   const double dist = sqrt(__dadd_rn(__dmul_rn(x, x), __dadd_rn(__dmul_rn(y, y), __dmul_rn(z, z))));
   if (dist > R) { idx[i] = -1; if (d2) d2[i] = INFINITY; }
 }
+
+// phase 1: one thread per (cell-sorted) query; uncertified queries go to the far queue
+// queue entry of an uncertified query: its state after phase 1 and its record, so that phase 2 starts from ONE
+// aligned 32-byte load instead of the dependent chain far[e] -> qrec[i]
+struct __align__(16) FarItem { unsigned long long best; uint32_t i; uint32_t pad; float4 rec; };
 
 template <int K1>
 __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridView g, const float4* __restrict__ qrec,
@@ -421,7 +454,7 @@ __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridVie
     if (lane == leader) base = atomicAdd(far_count, (unsigned)__popc(m));
     base = __shfl_sync(act, base, leader);
     if (!resolved) {
-      FarItem it; it.best = Q.best; it.i = i; it.pad = 1; it.rec = Q.record();
+      FarItem it; it.best = Q.best; it.i = i; it.pad = 0; it.rec = Q.record();
       far[base + __popc(m & ((1u << lane) - 1u))] = it;
     }
   }
@@ -471,55 +504,46 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   RadiusSrc rs;
   rs.radius = d_radius; rs.opt_num = d_opt_num; rs.fixed = fixed_radius;
   rs.max_r = sweep ? sweep->max_r : 0; rs.min_r = sweep ? sweep->min_r : 0; rs.drop = sweep ? sweep->drop : 0;
+  PCD_CUDA(ctx, ctx->qrec.ensure(16 * (size_t)n));
+  float4* qrec = ctx->qrec.as<float4>();
+  {
+    ProfScope ps(ctx, PCD_K_NN_KEYSORT, st);
+    const bool sorted = n > 2048;
+    if (sorted) {
+      PCD_CUDA(ctx, ctx->keys.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->keys_alt.ensure(4 * (size_t)n));
+      PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->vals_alt.ensure(4 * (size_t)n));
+    }
+    cub::DoubleBuffer<uint32_t> kb(ctx->keys.as<uint32_t>(), ctx->keys_alt.as<uint32_t>());
+    cub::DoubleBuffer<uint32_t> vb(ctx->vals.as<uint32_t>(), ctx->vals_alt.as<uint32_t>());
+    k_query_keys<<<pcd_blocks(n, 256), 256, 0, st>>>(d_q, rs, n, g, sorted ? kb.Current() : nullptr, sorted ? vb.Current() : nullptr, qrec);
+    PCD_LAUNCH_CHECK(ctx);
+    if (sorted) {
+      int bits = 1; while (((int64_t)1 << bits) < cloud->n_cells && bits < 32) bits++;
+      // The order only has to make neighbouring lanes touch neighbouring cells: the lowest key bits (position
+      // inside a short x stretch) may stay unsorted when that saves a whole 8-bit radix pass.
+      int skip = 0;
+      if (const char* e = getenv("PCD_B200_SORT_SKIP")) skip = atoi(e);
+      else if (bits > 24 && bits <= 28) skip = bits - 24;
+      if (skip < 0 || skip >= bits) skip = 0;
+      size_t tmp = 0;
+      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, kb, vb, (int)n, skip, bits, st));
+      PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+      PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, kb, vb, (int)n, skip, bits, st));
+      order = vb.Current();
+    }
+  }
   PCD_CUDA(ctx, ctx->far_q.ensure(sizeof(FarItem) * (size_t)n + 16));
   unsigned int* far_count = ctx->far_q.as<unsigned int>();
   FarItem* far = (FarItem*)(ctx->far_q.as<char>() + 16);
-  PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 8, st));      // queue length and the work counter of the far search
-  // Large batches: tile-staged search (nn_tile.cu).  Small ones (and grids the tile path does not take): the
-  // thread-per-query search over global memory, cell-sorted when that pays.
-  bool tiled = false;
-  const char* menv = getenv("PCD_B200_NN_MODE");              // "cell" forces the thread-per-query search
-  if (n > 4096 && !(menv && menv[0] == 'c')) {
-    int rc = nn_tile_search(cloud, d_q, rs, n, d_idx, d2, far, far_count, st, &tiled);
-    if (rc) return rc;
-  }
-  if (!tiled) {
-    PCD_CUDA(ctx, ctx->qrec.ensure(16 * (size_t)n));
-    float4* qrec = ctx->qrec.as<float4>();
-    {
-      ProfScope ps(ctx, PCD_K_NN_KEYSORT, st);
-      const bool sorted = n > 2048;
-      if (sorted) {
-        PCD_CUDA(ctx, ctx->keys.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->keys_alt.ensure(4 * (size_t)n));
-        PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->vals_alt.ensure(4 * (size_t)n));
-      }
-      cub::DoubleBuffer<uint32_t> kb(ctx->keys.as<uint32_t>(), ctx->keys_alt.as<uint32_t>());
-      cub::DoubleBuffer<uint32_t> vb(ctx->vals.as<uint32_t>(), ctx->vals_alt.as<uint32_t>());
-      k_query_keys<<<pcd_blocks(n, 256), 256, 0, st>>>(d_q, rs, n, g, sorted ? kb.Current() : nullptr, sorted ? vb.Current() : nullptr, qrec);
-      PCD_LAUNCH_CHECK(ctx);
-      if (sorted) {
-        int bits = 1; while (((int64_t)1 << bits) < cloud->n_cells && bits < 32) bits++;
-        // The order only has to make neighbouring lanes touch neighbouring cells: the lowest key bits (position
-        // inside a short x stretch) may stay unsorted when that saves a whole 8-bit radix pass.
-        int skip = 0;
-        if (const char* e = getenv("PCD_B200_SORT_SKIP")) skip = atoi(e);
-        else if (bits > 24 && bits <= 28) skip = bits - 24;
-        if (skip < 0 || skip >= bits) skip = 0;
-        size_t tmp = 0;
-        PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, kb, vb, (int)n, skip, bits, st));
-        PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
-        PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, kb, vb, (int)n, skip, bits, st));
-        order = vb.Current();
-      }
-    }
-    const int blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
+  const int blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
+  {
     ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
+    PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 8, st));    // queue length and the work counter of phase 2
     if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
     else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
     PCD_LAUNCH_CHECK(ctx);
   }
-  const char* fenv = getenv("PCD_B200_FAR");                  // "legacy" = the lane-group far search
-  if (fenv && fenv[0] == 'l') {
+  {
     static int far_occ = 0;                                  // resident blocks per SM of k_nn_far
     if (far_occ == 0) {
       PCD_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&far_occ, k_nn_far, NN_THREADS, 0));
@@ -529,18 +553,6 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
     if ((int64_t)far_blocks * (NN_THREADS / FAR_GROUP) > n) far_blocks = (int)((n + NN_THREADS / FAR_GROUP - 1) / (NN_THREADS / FAR_GROUP));
     ProfScope psf(ctx, PCD_K_NN_FAR, st);
     k_nn_far<<<far_blocks, NN_THREADS, 0, st>>>(g, d_idx, d2, far, far_count, far_count + 1);
-    PCD_LAUNCH_CHECK(ctx);
-  } else {
-    static int far_occ = 0;
-    far2_tables_init(ctx->device);
-    if (far_occ == 0) {
-      PCD_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&far_occ, k_nn_far2, NN_THREADS, 0));
-      if (far_occ < 1) far_occ = 1;
-    }
-    int far_blocks = ctx->sm_count * far_occ;                // one resident wave; warps pull 32 queries at a time
-    if ((int64_t)far_blocks * NN_THREADS > n) far_blocks = (int)((n + NN_THREADS - 1) / NN_THREADS);
-    ProfScope psf(ctx, PCD_K_NN_FAR, st);
-    k_nn_far2<<<far_blocks, NN_THREADS, 0, st>>>(g, d_idx, d2, far, far_count, far_count + 1);
     PCD_LAUNCH_CHECK(ctx);
   }
   if (exact_radius && (d_radius || d_opt_num || fixed_radius != INFINITY)) {
