@@ -13,7 +13,9 @@ are replicated on every GPU, the queries are sharded (weak scaling: Q per GPU is
 the only exchange is an all-reduce of sum r^2 and the accepted counters.
 
 Workload (BASELINE.json configs[4]): queries against a 50 M-point cloud, the configuration the
-metric "at 1/2/4/8 B200" is quoted on.  --workload smith runs configs[1] (1 M cloud, 50 k points).
+metric "at 1/2/4/8 B200" is quoted on.  --workload smith runs configs[1] (1 M cloud, 50 k points);
+--workload zbuf450 runs configs[3] as written (10 M cloud into 450 images of 1920x1080, images sharded over the ranks,
+depth_image_scale 1.0 and the reference's 0.2) and prints a depth-projection line with a z-buffer roofline.
 """
 import argparse
 import json
@@ -30,9 +32,11 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as entry  # noqa: E402
 
 ALG_BYTES_NN = 260.0       # 12 B query + 8 B result + one 15-point leaf x 16 B
-# dram__bytes_read.sum + dram__bytes_write.sum of k_nn_search + k_nn_far from the one `ncu --set full` capture of the
-# default workload (profiles/r01_ncu_nn_v6_summary.txt: 3.709 + 0.777 + 0.710 + 0.071 GB for 16 M queries)
+# dram__bytes_read.sum + dram__bytes_write.sum of k_nn_search + k_nn_far per launch pair, from the `ncu --set full` capture
+# of the default workload named in NCU_TRAFFIC_SOURCE (the kernels are unchanged since that capture); None for any other
+# workload or size
 NCU_TRAFFIC_NN_SWEEP50M = 5.267e9
+NCU_TRAFFIC_SOURCE = "profiles/r01_ncu_nn_v6_summary.txt (3.709 + 0.777 GB k_nn_search, 0.710 + 0.071 GB k_nn_far, 16 M queries)"
 ALG_BYTES_RECORD = 56.0
 ALG_BYTES_RESJAC = 96.0
 WEIGHTS = (10.0, 1000.0, 10000.0)          # proj / icp / icp_ground (src/controllers/incremental_mapper.h:74-78)
@@ -44,6 +48,7 @@ WORKLOADS = {
     "full10m": (10_000_000, 1_000_000, "configs[2]: 10M-pt cloud, 1M SfM points"),
     "full10m_sweep": (10_000_000, 1_000_000, "configs[2]: 10M-pt cloud, 1M SfM points, the full 14-pass kdtree search-range drop sweep per step"),
     "smith": (1_000_000, 50_000, "configs[1]: Smith-Hall-shaped scene, 1M-pt cloud, 50k SfM points"),
+    "zbuf450": (10_000_000, 0, "configs[3]: depth-projection z-buffer, 10M-pt cloud into 450 images at 1920x1080, images sharded over the ranks"),
 }
 
 
@@ -128,6 +133,15 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def host_threads():
+    """Threads the CPU arm may use: the cores this process is allowed on.  torch.distributed.run exports
+    OMP_NUM_THREADS=1, so omp_get_max_threads() is not the answer; the count is passed to the oracle explicitly."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def load_mods():
     pcd = entry.package()
     synth = entry._load("pcd_synth", os.path.join(entry.PKG, "synth.py"))
@@ -152,12 +166,16 @@ def workload_sizes(args):
     return n_cloud, q, desc
 
 
+def passes_per_step(args):
+    return 14 if args.workload.endswith("_sweep") else 1     # ranges 1.5, 1.4 ... 0.2: GlobalOptNum += 1 per pass
+
+
 def base_line(args, n_cloud, q_per_gpu, desc, world):
     return {"metric": "ICP association queries/s (NN + LidarPoint record + residual/Jacobian pass)", "unit": "queries/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32 NN distance / f64 record, residual, Jacobian", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc}", "cloud_points": n_cloud, "queries_per_gpu": q_per_gpu,
-                       "queries_total": q_per_gpu * world, "radius_sweep": list(SWEEP), "variant": "global (incremental_mapper.cc:1430-1468)",
+                       "queries_total": q_per_gpu * world, "passes_per_step": passes_per_step(args), "radius_sweep": list(SWEEP), "variant": "global (incremental_mapper.cc:1430-1468)",
                        "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
                        "parallelism": f"queries sharded x{world}, cloud+index replicated",
                        "exchange": "none (1 GPU)" if world == 1 else
@@ -182,7 +200,7 @@ def cpu_pass(orc, tree, q, rng, threads):
 def pick_threads(orc, tree, q, rng):
     """All host threads unless a probe shows fewer are faster (cgroup-limited boxes oversubscribe)."""
     best, best_t = 1, None
-    cand = sorted({1, max(1, orc.max_threads() // 2), orc.max_threads()})
+    cand = sorted({1, max(1, host_threads() // 2), host_threads()})
     for th in cand:
         cpu_pass(orc, tree, q[:20_000], rng[:20_000], th)
         ta, tr, _, _ = cpu_pass(orc, tree, q, rng, th)
@@ -209,16 +227,19 @@ def cpu_baseline(orc, world_cloud, q, opt_num, seconds):
             "assoc_queries_per_s": m / ta, "resjac_evals_per_s": m / tr, "accepted_frac": float(rec["accepted"].mean())}, tree
 
 
-def zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, n_img, rank, world, scale=1.0):
+def zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, n_img, rank, world, scale=1.0, total_images=None, dense_images=1):
     """Secondary metric (SURVEY.md 8d, configs[3]): depth projection of the resident cloud into this rank's images at
-    1920x1080, depth_image_scale 1.0, 3000 keypoints each -- PcdProj::SetNewImage through the host-pointer C ABI
-    (feature z-buffer, winners copied back), plus one dense z-buffer (the if_save_depth_image map)."""
+    1920x1080, 3000 keypoints each -- PcdProj::SetNewImage through the host-pointer C ABI (feature z-buffer, winners
+    copied back), plus dense z-buffers (the if_save_depth_image map).  The z-buffer's bound is the L2's 64-bit atomic
+    rate: `roofline` divides the dense kernel's atomicMin rate by a contention-free coalesced sweep measured in the
+    same run (pcd_atomic_peak)."""
     opt = pcd.ProjOptions.default(depth_image_scale=scale)
     t0 = time.perf_counter()
     cloud.build_submap(opt)
     t_sub = time.perf_counter() - t0
     shard = load_shard()
-    cams = synth.make_cameras(n_img * world, synth.scene_extent(n_cloud), cam=synth.OPENCV_1080)
+    n_all = total_images if total_images is not None else n_img * world
+    cams = synth.make_cameras(n_all, synth.scene_extent(n_cloud), cam=synth.OPENCV_1080)
     mine = [cams[k] for k in shard.shard_images(len(cams), world, rank)]
     imgs = [pcd.Image.make(c["qvec"], c["tvec"], c["cam"], c["width"], c["height"]) for c in mine]
     coef = pcd.splat_coef(cams[0]["cam"], opt)
@@ -231,16 +252,68 @@ def zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, n_img, rank, world, scale=1.0):
     dt = time.perf_counter() - t0
     k_ms, k_n = ctx.kernel_time(pcd.K_PROJECT)
     ctx.profile(False)
+    w, h = int(1920 * scale), int(1080 * scale)
+    peak = ctx.atomic_peak(w * h, 64)
+    cloud.project_image(imgs[0], coef, None, dense=True)                         # warm-up of the dense kernel
+    ctx.profile(True)
     t0 = time.perf_counter()
-    _, _, z, dstats = cloud.project_image(imgs[0], coef, None, dense=True)
+    atom = 0; covered = 0
+    for im in imgs[:dense_images]:
+        _, _, z, dstats = cloud.project_image(im, coef, None, dense=True)
+        atom += int(dstats[2]); covered += int((z != np.iinfo(np.uint64).max).sum())
     dt_dense = time.perf_counter() - t0
+    dk_ms, dk_n = ctx.kernel_time(pcd.K_PROJECT)
+    ctx.profile(False)
+    rate = atom / max(1e-3 * dk_ms, 1e-12)
     return {"images": len(imgs), "image_size": [1920, 1080], "depth_image_scale": scale, "features_per_image": len(feats),
-            "submap_build_s": t_sub, "images_per_s": len(imgs) / dt, "point_projections_per_s": float(stats[1]) / dt,
+            "submap_build_s": t_sub, "seconds": dt, "images_per_s": len(imgs) / dt, "point_projections_per_s": float(stats[1]) / dt,
             "pixel_updates_per_s": float(stats[2]) / dt, "points_projected": int(stats[1]), "pixel_updates": int(stats[2]),
             "features_hit": int(stats[3]), "k_project_ms_per_image": k_ms / max(k_n, 1),
             "k_project_point_bytes_GBps": 16.0 * float(stats[1]) / max(k_ms * 1e-3, 1e-12) / 1e9,
-            "dense": {"seconds": dt_dense, "pixels_covered": int((z != np.iinfo(np.uint64).max).sum()),
-                      "pixel_atomics": int(dstats[2]), "pixel_atomics_per_s": float(dstats[2]) / dt_dense}}
+            "dense": {"images": int(dk_n), "seconds": dt_dense, "pixels_covered": covered, "pixel_atomics": atom,
+                      "k_project_dense_ms_per_image": dk_ms / max(dk_n, 1), "pixel_atomics_per_s_wall": atom / dt_dense},
+            "roofline": {"bound": "l2-atomics", "kernel": "k_project<DENSE> (one 64-bit atomicMin per covered pixel)",
+                         "achieved": rate / 1e9, "peak": peak / 1e9, "unit": "G atomicMin/s", "frac": rate / peak,
+                         "peak_source": f"pcd_atomic_peak: contention-free warp-coalesced 64-bit atomicMin over one {w}x{h} z-buffer, 64 sweeps, "
+                                        "CUDA events, measured in this run",
+                         "atomics_per_launch": atom // max(dk_n, 1), "avg_launch_ms": dk_ms / max(dk_n, 1), "launches_timed": int(dk_n)}}
+
+
+def run_zbuf450(args, pcd, synth, ctx, cloud, n_cloud, rank, world, dev, t_gen, t_build):
+    """configs[3] as written: the 10 M-point cloud into 450 images of 1920x1080, images sharded 57/56 over 8 ranks
+    (round-robin), at depth_image_scale 1.0 and at the reference's default 0.2.  value = images/s of the whole job
+    through the host-pointer C ABI (PcdProj::SetNewImage per image: feature mask up, winners back), max over ranks."""
+    import torch
+    import torch.distributed as dist
+    out = {}
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+    if rank == 0:
+        sampler.start()
+    for scale in (1.0, 0.2):
+        zb = zbuffer_leg(pcd, synth, ctx, cloud, n_cloud, 0, rank, world, scale, total_images=450, dense_images=4)
+        t = torch.tensor([zb["seconds"]], dtype=torch.float64, device=dev)
+        tot = torch.tensor([float(zb["points_projected"]), float(zb["pixel_updates"]), float(zb["images"])], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        zb["job_seconds_max_over_ranks"] = float(t.item())
+        zb["job_images_per_s"] = float(tot[2].item()) / float(t.item())
+        zb["job_point_projections_per_s"] = float(tot[0].item()) / float(t.item())
+        zb["job_pixel_updates_per_s"] = float(tot[1].item()) / float(t.item())
+        out[f"scale_{scale}"] = zb
+    clocks = sampler.stop() if rank == 0 else None
+    if rank == 0:
+        z1 = out["scale_1.0"]
+        line = {"metric": "depth-projection images/s (PcdProj::SetNewImage z-buffer, configs[3])", "unit": "images/s",
+                "value": z1["job_images_per_s"], "n_gpus": world, "steps": 1, "warmup": 1, "ms_per_step": 1e3 * z1["job_seconds_max_over_ranks"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 transform / f64 distortion / u64 packed atomicMin",
+                "data": "synthetic",
+                "config": {"workload": f"zbuf450: {WORKLOADS['zbuf450'][2]}", "cloud_points": n_cloud, "images_total": 450,
+                           "images_per_rank": z1["images"], "image_size": [1920, 1080], "features_per_image": 3000,
+                           "depth_image_scale": [1.0, 0.2], "parallelism": f"images round-robin x{world}, cloud + sub-map replicated"},
+                "clocks": clocks, "roofline": z1["roofline"], "scale_1.0": z1, "scale_0.2": out["scale_0.2"],
+                "setup_s": {"cloud_gen_and_replicate": t_gen, "upload_and_index_build": t_build}}
+        print(json.dumps(line), flush=True)
 
 
 def run_reference(args):
@@ -255,6 +328,39 @@ def run_reference(args):
     raw, _ = synth.make_cloud(n_cloud, seed=synth.SEED0 + 4)
     world_cloud = orc.direction_trans(raw)
     del raw
+    if args.workload == "zbuf450":
+        # the reference's sequential SetNewImage (sub-map + frustum + splat) on a bounded sample of the 450 images
+        opt = orc.ProjOptions.default(depth_image_scale=1.0)
+        sub = orc.Submap(world_cloud, opt)
+        cams = synth.make_cameras(450, synth.scene_extent(n_cloud), cam=synth.OPENCV_1080)
+        coef = orc.splat_coef(cams[0]["cam"], opt)
+        feats = synth.make_features(3000, cam=synth.OPENCV_1080)
+        fpix = orc.feature_pixels(feats, 1.0, 1920, 1080)
+        mask = np.zeros(1920 * 1080, np.uint8); mask[fpix[fpix >= 0]] = 1
+
+        def one(c):
+            sub.project(c["qvec"], c["tvec"], c["cam"], c["width"], c["height"], coef, feat_mask=mask)
+        t0 = time.perf_counter(); one(cams[0]); per = time.perf_counter() - t0
+        m = int(max(1, min(8, 90.0 / max(per, 1e-3) / max(1, args.steps + args.warmup))))
+        for _ in range(args.warmup):
+            for c in cams[:m]:
+                one(c)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            for c in cams[:m]:
+                one(c)
+        dt = time.perf_counter() - t0
+        value = m * args.steps / dt
+        print(json.dumps({"impl": "reference", "metric": "depth-projection images/s (PcdProj::SetNewImage z-buffer, configs[3])",
+                          "unit": "images/s", "value": value, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                          "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                          "dtype": "f32 transform / f64 distortion", "data": "synthetic", "gpu_launches": 0,
+                          "config": {"workload": f"zbuf450: {desc}", "cloud_points": n_cloud, "images_total": 450, "image_size": [1920, 1080],
+                                     "features_per_image": 3000, "depth_image_scale": [1.0]},
+                          "cpu_baseline": {"value": value, "unit": "images/s", "cores": 1, "kind": "port",
+                                           "sample": f"{m} of the 450 images per step, feature z-buffer, sequential like the race-free reading of the reference"},
+                          "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+        return
     tree = orc.KdTree(world_cloud)
     # bounded sample per step: sized from a probe so that the whole run ends within a few minutes
     qp, onp = synth.make_queries(world_cloud, 100_000, seed=synth.SEED0 + 100)
@@ -316,6 +422,12 @@ def run_b200(args):
     del d_raw
     info = cloud.build_index()
     t_build = time.perf_counter() - t_build
+    if args.workload == "zbuf450":
+        run_zbuf450(args, pcd, synth, ctx, cloud, n_cloud, rank, world, dev, t_gen, t_build)
+        cloud.close(); ctx.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
     world_cloud = cloud.download()          # host copy: query synthesis (and the CPU baseline on rank 0)
 
     # ---- this rank's shard of the SfM points (hash order), pinned for the end-to-end leg ------------
@@ -341,6 +453,7 @@ def run_b200(args):
     # residual / Jacobian outputs are double-buffered so that the exchange of pass k overlaps the kernels of pass k+1
     d_rb = [d_r, torch.empty_like(d_r)] if world > 1 else [d_r]
     d_Jb = [d_J, torch.empty_like(d_J)] if world > 1 else [d_J]
+    d_sumb = [d_sum, torch.zeros_like(d_sum)] if world > 1 else [d_sum]     # sum r^2 travels with its pass's blocks
     shard = load_shard()
     gather = None
     if world > 1:
@@ -355,7 +468,7 @@ def run_b200(args):
     flush = None if Q * 24 > 126e6 * 2 else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
 
-    passes = 14 if args.workload.endswith("_sweep") else 1     # ranges 1.5, 1.4 ... 0.2: GlobalOptNum += 1 per pass
+    passes = passes_per_step(args)
     d_on0 = d_on.clone()
 
     def step():
@@ -374,11 +487,11 @@ def run_b200(args):
         if world > 1:
             gather.wait_buffer(b)               # the exchange of pass k-2 read these buffers
         cloud.associate_evaluate_dev(d_q.data_ptr(), 0, d_on.data_ptr(), SWEEP, Q, pcd.ASSOC_GLOBAL, WEIGHTS, optrs,
-                                     d_rb[b].data_ptr(), d_Jb[b].data_ptr(), d_sum.data_ptr(), stream)
+                                     d_rb[b].data_ptr(), d_Jb[b].data_ptr(), d_sumb[b].data_ptr(), stream)
         if world > 1:
             # the path's one exchange step: all-gather of the residuals and Jacobian blocks and
             # all-reduce of sum r^2, NCCL over NVLink on a side stream
-            gather.start(d_rb[b], d_Jb[b], d_sum, b)
+            gather.start(d_rb[b], d_Jb[b], d_sumb[b], b)
 
     def barrier():
         if gather is not None:
@@ -491,10 +604,9 @@ def run_b200(args):
         ms_step = gpu_ms_max / args.steps
         line = base_line(args, n_cloud, Q, desc, world)
         peak, peak_src = measured_peak()
-        nn_ms, nn_n = ktime["K_NN_SEARCH"]
+        nn_ms, nn_n = ktime["K_NN_SEARCH"][0] + ktime["K_NN_FAR"][0], ktime["K_NN_SEARCH"][1]     # the two spans are timed apart
         nn_avg_s = 1e-3 * nn_ms / max(nn_n, 1)
         achieved = ALG_BYTES_NN * Q / nn_avg_s / 1e9
-        line["config"]["passes_per_step"] = passes
         if exchange_ok is not None:
             line["exchange_verified"] = exchange_ok
         line.update({"value": passes * Q * world / (ms_step * 1e-3), "ms_per_step": ms_step, "gpu_launches": int(launches),
@@ -502,16 +614,16 @@ def run_b200(args):
                      "e2e": None if args.no_e2e else {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
                              "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                              "api": "pcd_associate_evaluate_batch (host pointers, pinned; chunked H2D / kernels / D2H pipeline)"},
-                     "roofline": {"bound": "hbm", "kernel": "k_nn_search + k_nn_far (timed together)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "roofline": {"bound": "hbm", "kernel": "k_nn_search + k_nn_far (two CUDA-event spans per pass, added)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                   "frac": achieved / peak,
                                   "traffic": NCU_TRAFFIC_NN_SWEEP50M if (args.workload == "sweep50m" and Q == 16_000_000 and n_cloud == 50_000_000) else None,
-                                  "traffic_source": "profiles/r01_ncu_nn_v6_summary.txt (bytes per launch pair)", "peak_source": peak_src,
+                                  "traffic_source": NCU_TRAFFIC_SOURCE, "peak_source": peak_src,
                                   "algorithmic_bytes_per_query": ALG_BYTES_NN, "queries_per_launch": Q,
                                   "avg_launch_ms": 1e3 * nn_avg_s, "launches_timed": int(nn_n)},
                      "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktime.items()},
                      "kernels_note": "K_ASSOC_RECORD is the fused record + weight + cost-function kernel of the pass; K_RESJAC is the "
                                      "standalone cost-function kernel timed separately on the same matches (not part of ms_per_step)",
-                     "assoc_queries_per_s_per_gpu": passes * Q / (1e-3 * (ktime["K_NN_KEYSORT"][0] + ktime["K_NN_SEARCH"][0] + ktime["K_ASSOC_RECORD"][0]) / args.steps),
+                     "assoc_queries_per_s_per_gpu": passes * Q / (1e-3 * (ktime["K_NN_KEYSORT"][0] + ktime["K_NN_SEARCH"][0] + ktime["K_NN_FAR"][0] + ktime["K_ASSOC_RECORD"][0]) / args.steps),
                      "resjac_evals_per_s_per_gpu": Q / (1e-3 * ktime["K_RESJAC"][0] / max(ktime["K_RESJAC"][1], 1)),
                      "resjac_roofline_frac": ALG_BYTES_RESJAC * Q / (1e-3 * ktime["K_RESJAC"][0] / max(ktime["K_RESJAC"][1], 1)) / 1e9 / peak,
                      "accepted_frac": float(red[1].item()) / (Q * world), "sum_sq": float(red[2].item()),

@@ -105,7 +105,8 @@ __global__ void __launch_bounds__(256) k_assoc_record(const float4* __restrict__
     if (o.angle) o.angle[i] = angle;
     if (FUSED_EVAL) {
       double J[3] = {0.0, 0.0, 0.0};
-      if (acc) {
+      // a NaN plane coefficient (e.g. an infinite normal) adds no residual block: bundle_adjustment.cc:1003-1007
+      if (acc && !(isnan(abcd[0]) || isnan(abcd[1]) || isnan(abcd[2]) || isnan(abcd[3]))) {
         const double w = type == PCD_TYPE_PROJ ? ev.wp : (type == PCD_TYPE_ICP ? ev.wi : (type == PCD_TYPE_ICP_GROUND ? ev.wg : 0.0));
         double s = ((px * abcd[0] + py * abcd[1]) + pz * abcd[2]) + abcd[3];
         double u = 0.0 - s;

@@ -222,87 +222,14 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
   }
 }
 
-// Experimental variant of the feature-mask path (selected by PCD_B200_PROJ_COOP=<pixels>, default off; A/B tool:
-// tools/explore_proj.py).  Points near the camera have splats of tens of thousands of pixels, and the lane that owns
-// one walks all its mask words alone while 31 lanes wait.  Here a splat larger than `coop_px` pixels is handed to the
-// whole warp: the (row group, mask word) tiles of its rectangle are dealt round-robin to the lanes.  Winners are
-// unchanged (atomicMin commutes).
-__device__ __forceinline__ void mask_tile(const uint32_t* __restrict__ mask, const uint32_t* __restrict__ summ,
-                                          unsigned long long* __restrict__ zbuf, const ImgParams& P, int vg, int wd, int ua,
-                                          int ub, int va, int vb, unsigned long long packed) {
-  uint32_t any = __ldg(&summ[(int64_t)vg * P.words + wd]);
-  if (!any) return;
-  const int lo = max(ua - (wd << 5), 0), hi = min(ub - (wd << 5), 31);
-  const uint32_t m = (hi == 31 ? 0xffffffffu : ((1u << (hi + 1)) - 1u)) & ~((1u << lo) - 1u);
-  if (!(any & m)) return;
-  const int v1 = min(vb, (vg << MASK_ROWS_LOG2) + MASK_ROWS - 1);
-  for (int v = max(va, vg << MASK_ROWS_LOG2); v <= v1; v++) {
-    uint32_t bits = __ldg(&mask[(int64_t)v * P.words + wd]) & m;
-    while (bits) {
-      const int bpos = __ffs(bits) - 1; bits &= bits - 1;
-      unsigned long long* px = zbuf + (int64_t)v * P.w + (wd << 5) + bpos;
-      if (packed < *px) atomicMin(px, packed);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256) k_project_coop(SubmapView sm, ImgParams P, const uint32_t* __restrict__ mask,
-                                                      const uint32_t* __restrict__ summ, unsigned long long* __restrict__ zbuf,
-                                                      unsigned long long* __restrict__ stats, int coop_px) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  unsigned long long n_pts = 0, n_px = 0, n_cells = 0;
-  for (int64_t s = warp; s < sm.n_seg; s += nwarps) {
-    const uint2 sg = __ldg(&sm.seg[s]);
-    const int64_t c = sg.x;
-    float x = (float)sm.keys[3 * c] * sm.len, y = (float)sm.keys[3 * c + 1] * sm.height, z = (float)sm.keys[3 * c + 2] * sm.width;
-    bool in = true;
-#pragma unroll
-    for (int k = 0; k < 5; k++) {
-      float v = P.planes[4 * k] * x + P.planes[4 * k + 1] * y;
-      v = v + P.planes[4 * k + 2] * z;
-      v = v + P.planes[4 * k + 3];
-      in = in && (v <= 0.0f);
-    }
-    if (!in) continue;
-    const uint32_t b = sg.y, e = min(b + sm.seg_len, sm.start[c + 1]);
-    if (lane == 0 && b == sm.start[c]) n_cells++;
-    for (uint32_t j0 = b; j0 < e; j0 += 32) {
-      const uint32_t j = j0 + lane;
-      unsigned long long packed = 0;
-      int ua = 0, ub = -1, va = 0, vb = -1;
-      const bool rect = j < e && point_rect(P, __ldg(&sm.pts[j]), packed, ua, ub, va, vb, n_pts, n_px);
-      const bool big = rect && (int64_t)(ub - ua + 1) * (vb - va + 1) > coop_px;
-      if (rect && !big) {
-        for (int vg = va >> MASK_ROWS_LOG2; vg <= (vb >> MASK_ROWS_LOG2); vg++)
-          for (int wd = ua >> 5; wd <= (ub >> 5); wd++) mask_tile(mask, summ, zbuf, P, vg, wd, ua, ub, va, vb, packed);
-      }
-      unsigned todo = __ballot_sync(0xffffffffu, big);
-      while (todo) {
-        const int src = __ffs(todo) - 1; todo &= todo - 1;
-        const unsigned long long pk = __shfl_sync(0xffffffffu, packed, src);
-        const int a0 = __shfl_sync(0xffffffffu, ua, src), a1 = __shfl_sync(0xffffffffu, ub, src);
-        const int r0 = __shfl_sync(0xffffffffu, va, src), r1 = __shfl_sync(0xffffffffu, vb, src);
-        const int w0 = a0 >> 5, nW = (a1 >> 5) - w0 + 1, g0 = r0 >> MASK_ROWS_LOG2;
-        const int tot = nW * ((r1 >> MASK_ROWS_LOG2) - g0 + 1);
-        for (int t = lane; t < tot; t += 32) {
-          const int gi = t / nW;
-          mask_tile(mask, summ, zbuf, P, g0 + gi, w0 + (t - gi * nW), a0, a1, r0, r1, pk);
-        }
-      }
-    }
-  }
-  if (stats) {
-    for (int o = 16; o > 0; o >>= 1) {
-      n_pts += __shfl_down_sync(0xffffffffu, n_pts, o);
-      n_px += __shfl_down_sync(0xffffffffu, n_px, o);
-    }
-    if (lane == 0) {
-      if (n_cells) atomicAdd(&stats[0], n_cells);
-      if (n_pts) atomicAdd(&stats[1], n_pts);
-      if (n_px) atomicAdd(&stats[2], n_px);
-    }
+// Reference point for the z-buffer's roofline: 64-bit atomicMin on a buffer the size of one z-buffer, no two
+// threads on one word at a time, lanes of a warp on 32 consecutive words (the access pattern of the dense splat),
+// every operation a real update (values fall with each sweep).
+__global__ void k_atomic_sweep(unsigned long long* __restrict__ buf, int64_t words, int sweeps) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int s = 0; s < sweeps; s++) {
+    const unsigned long long v = ((unsigned long long)(0x7f000000u - (unsigned)s) << 32) | (unsigned)s;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < words; i += stride) atomicMin(&buf[i], v);
   }
 }
 
@@ -373,10 +300,7 @@ static int project_one(pcd_cloud* c, const pcd_image* img, const double coef[4],
     int blocks = (int)((warps + 7) / 8);
     int cap = ctx->sm_count * 16; if (blocks > cap) blocks = cap;
     ProfScope ps(ctx, PCD_K_PROJECT, st);
-    int coop_px = 0;                                          // experimental variant, off unless asked for
-    if (!dense) { if (const char* e = getenv("PCD_B200_PROJ_COOP")) coop_px = atoi(e); }
     if (dense) k_project<true><<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats);
-    else if (coop_px > 0) k_project_coop<<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats, coop_px);
     else k_project<false><<<blocks, 256, 0, st>>>(sm, P, mask, summ, zb, d_stats);
     PCD_LAUNCH_CHECK(ctx);
   }
@@ -405,6 +329,36 @@ int pcd_splat_coef(const double cam[8], const pcd_proj_options* o, double coef[4
   double a_y = (max_y - min_y) / (o->min_proj_dist - (double)o->choose_meter);
   double b_y = (double)o->min_proj_scale - a_y * (double)o->choose_meter;   // quirk F7: raw min_proj_scale
   coef[0] = a_x; coef[1] = b_x; coef[2] = a_y; coef[3] = b_y;
+  return PCD_OK;
+}
+
+int pcd_atomic_peak(pcd_ctx* ctx, int64_t words, int sweeps, double* atomics_per_s) {
+  if (!ctx || !atomics_per_s || words <= 0 || sweeps <= 0) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_atomic_peak: bad argument");
+  DeviceGuard g(ctx->device);
+  cudaStream_t st = ctx->stream;
+  PCD_CUDA(ctx, ctx->zbuf.ensure(8 * (size_t)words));
+  unsigned long long* buf = ctx->zbuf.as<unsigned long long>();
+  cudaEvent_t a = nullptr, b = nullptr;
+  PCD_CUDA(ctx, cudaEventCreate(&a));
+  cudaError_t e = cudaEventCreate(&b);
+  if (e != cudaSuccess) { cudaEventDestroy(a); PCD_CUDA(ctx, e); }
+  const int blocks = ctx->sm_count * 8;
+  float best = 0.0f;
+  for (int rep = 0; rep < 4 && e == cudaSuccess; rep++) {       // first repetition warms up; best of the rest
+    e = cudaMemsetAsync(buf, 0xff, 8 * (size_t)words, st);
+    if (e == cudaSuccess) e = cudaEventRecord(a, st);
+    pcd::k_atomic_sweep<<<blocks, 256, 0, st>>>(buf, words, sweeps);
+    ctx->launches++;
+    if (e == cudaSuccess) e = cudaEventRecord(b, st);
+    if (e == cudaSuccess) e = cudaEventSynchronize(b);
+    float ms = 0.0f;
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, a, b);
+    if (e == cudaSuccess && rep > 0 && (best == 0.0f || ms < best)) best = ms;
+  }
+  if (e == cudaSuccess) e = cudaGetLastError();
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  PCD_CUDA(ctx, e);
+  *atomics_per_s = (double)words * sweeps / (1e-3 * (double)best);
   return PCD_OK;
 }
 

@@ -8,8 +8,11 @@
 namespace pcd {
 
 // residual + Jet derivative for one constraint. J = NaN at u == 0 (0 * inf), as autodiff gives.
+// A plane with a NaN coefficient never becomes a residual block (AddLidarToProblem returns before Create,
+// src/optim/bundle_adjustment.cc:1003-1007): its row is reported like a rejected match, r = 0 and J = 0.
 __device__ __forceinline__ void eval_lidar(double p0, double p1, double p2, double a, double b, double c, double d,
                                            double w, double& r, double J[3]) {
+  if (isnan(a) || isnan(b) || isnan(c) || isnan(d)) { r = 0.0; J[0] = J[1] = J[2] = 0.0; return; }
   double s = ((p0 * a + p1 * b) + p2 * c) + d;
   double u = 0.0 - s;
   double f = u * u;

@@ -125,6 +125,12 @@ class Context:
         self.check(lib().pcd_ctx_kernel_time(self._h, C.c_int(which), C.byref(ms), C.byref(n)), "pcd_ctx_kernel_time")
         return ms.value, n.value
 
+    def atomic_peak(self, words=1920 * 1080, sweeps=64):
+        """Contention-free, warp-coalesced 64-bit atomicMin updates per second (the z-buffer's roofline denominator)."""
+        v = C.c_double()
+        self.check(lib().pcd_atomic_peak(self._h, C.c_int64(words), C.c_int(sweeps), C.byref(v)), "pcd_atomic_peak")
+        return v.value
+
     def weights_from_type_dev(self, d_type, n, w_proj, w_icp, w_ground, d_w, stream=0):
         self.check(lib().pcd_weights_from_type_dev(self._h, C.c_void_p(d_type), C.c_int64(n), C.c_double(w_proj),
                                                    C.c_double(w_icp), C.c_double(w_ground), C.c_void_p(d_w),

@@ -83,7 +83,7 @@ enum {
   PCD_K_ASSOC_RECORD = 2, /* k_assoc_record                                     */
   PCD_K_RESJAC = 3,       /* k_resjac (+ partial-sum reduction)                 */
   PCD_K_PROJECT = 4,      /* k_project (z-buffer splat)                         */
-  PCD_K_NN_FAR = 5,       /* k_nn_far (far queries; also inside PCD_K_NN_SEARCH) */
+  PCD_K_NN_FAR = 5,       /* k_nn_far (far queries; timed apart from k_nn_search) */
   PCD_K_COUNT = 8
 };
 PCD_API int pcd_ctx_profile(pcd_ctx* ctx, int enable);
@@ -223,6 +223,11 @@ PCD_API int64_t pcd_submap_cells(const pcd_cloud* cloud);
 /* The function-local statics a_x b_x a_y b_y of src/lidar/pcd_projection.cc:391-397, computed
  * from the first camera projected in the process (quirk F7). */
 PCD_API int pcd_splat_coef(const double cam[8], const pcd_proj_options* opt, double coef[4]);
+
+/* Measurement aid for the z-buffer's roofline (north_star: "atomic throughput for the z-buffer"): the rate of
+ * contention-free, warp-coalesced 64-bit atomicMin updates on a buffer of `words` words (one z-buffer), `sweeps`
+ * passes, timed with CUDA events; best of three. */
+PCD_API int pcd_atomic_peak(pcd_ctx* ctx, int64_t words, int sweeps, double* atomics_per_s);
 
 typedef struct pcd_image {
   double qvec[4];      /* Image::Qvec()  (w x y z)                                   */

@@ -431,6 +431,11 @@ ORC_API int orc_match_proj(const double* p, const double* cand, int n_cand,
 ORC_API void orc_resjac(const double* p, const double* abcd, const double* w, int64_t n, double* r, double* J) {
   for (int64_t i = 0; i < n; i++) {
     const double* P = p + 3 * i; const double* A = abcd + 4 * i;
+    if (isnan(A[0]) || isnan(A[1]) || isnan(A[2]) || isnan(A[3])) {   /* no residual block: bundle_adjustment.cc:1003-1007 */
+      r[i] = 0.0;
+      if (J) J[3 * i] = J[3 * i + 1] = J[3 * i + 2] = 0.0;
+      continue;
+    }
     double s = ((P[0] * A[0] + P[1] * A[1]) + P[2] * A[2]) + A[3];
     double u = 0.0 - s;
     double f = u * u;

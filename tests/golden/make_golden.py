@@ -14,10 +14,15 @@ outputs of the reference: parity stays "unpinned".  What they give instead:
                    src/lidar/lidar_point.cc:21-50) and the Jet<double,3> rules for the cost
                    function (src/base/cost_functions.h:204-232).  Both the C oracle (CPU suite) and
                    the CUDA path (GPU suite) are checked against it.
-  zbuf_small.npz   a REGRESSION pin of the depth-projection z-buffer: produced by the C oracle
-                   itself (sequential reading of src/lidar/pcd_projection.cc:258-559), so it only
-                   guards against drift; the independent check of the z-buffer is
-                   tests/test_cpu.py::test_zbuffer_sequential_properties.
+  zbuf_small.npz   an INDEPENDENT numpy restatement of the depth projection too
+                   (tests/golden/proj_numpy.py, written from src/lidar/pcd_projection.cc:258-594 and
+                   pcd_projection.h:67-158, not from the oracle): frustum planes, cell selection,
+                   float32 transform, fp64 distortion, rounding, depth-dependent splat incl. the b_y
+                   quirk, min range with the first-visited / lowest-index tie rule.  Four images: two at
+                   the reference's depth_image_scale 0.2 (4032x3024, distorted), two at 1.0
+                   (1920x1080), one of them with an identity pose and hand-placed points at
+                   min_proj_dist, one float above it, nearer than min_lidar_proj_dist and behind the
+                   camera.  Dense packed z-buffers (range bits << 32 | winner) and feature winners.
 """
 import hashlib
 import os
@@ -127,33 +132,71 @@ def main():
     np.savez_compressed(os.path.join(HERE, "assoc_small.npz"), **out)
     print("assoc_small.npz:", len(world), "points,", len(q), "queries,", int(acc.sum()), "accepted (global variant)")
 
-    # ---- z-buffer regression pin (produced by the C oracle) -------------------------------------
-    orc = load("orc", os.path.join(ROOT, "oracle", "orc.py"))
+    # ---- z-buffer: independent numpy restatement (tests/golden/proj_numpy.py) ------------------
+    pn = load("proj_numpy", os.path.join(HERE, "proj_numpy.py"))
     raw2, info2 = synth.make_cloud(20_000, seed=SEED + 7)
-    world2 = orc.direction_trans(raw2)
-    opt = orc.ProjOptions.default()
-    sub = orc.Submap(world2, opt)
+    world2 = direction_trans(raw2)
+    # hand-placed points for the identity-pose camera (camera frame = world frame): exactly at min_proj_dist (near
+    # branch, :402-405), one float above it (linear branch), nearer than min_lidar_proj_dist (skipped, :400), behind
+    extra = np.zeros((5, 8), np.float32)
+    extra[:, 0:3] = [[0.1, 0.2, 2.0], [-0.2, 0.1, np.nextafter(np.float32(2.0), np.float32(3.0))], [0.0, 0.1, 0.3], [0.05, 0.0, -1.0],
+                     [0.1, 0.05, 0.5]]
+    extra[:, 4:7] = [0.0, 0.0, -1.0]
+    world2 = np.concatenate([world2, extra]).astype(np.float32)
+    # back to the lidar frame so that the fixture is fed through the loader like any cloud: inverse of (x,y,z) <- (-y,-z,x)
+    raw2 = np.zeros_like(world2)
+    raw2[:, 0], raw2[:, 1], raw2[:, 2] = world2[:, 2], -world2[:, 0], -world2[:, 1]
+    raw2[:, 4], raw2[:, 5], raw2[:, 6] = world2[:, 6], -world2[:, 4], -world2[:, 5]
+    assert np.array_equal(direction_trans(raw2).view(np.uint32), world2.view(np.uint32))
     cams = synth.make_cameras(3, info2)
-    coef = orc.splat_coef(cams[0]["cam"], opt)
-    z = {}
-    for k, cam in enumerate(cams):
-        zb, _, _ = sub.project(cam["qvec"], cam["tvec"], cam["cam"], cam["width"], cam["height"], coef)
+    ident = dict(qvec=np.array([1.0, 0.0, 0.0, 0.0]), tvec=np.zeros(3), cam=list(synth.OPENCV_1080["cam"]), width=1920, height=1080)
+    runs = [(cams[0], 0.2), (cams[1], 0.2), (ident, 1.0), (dict(cams[2], cam=list(synth.OPENCV_1080["cam"]), width=1920, height=1080), 1.0)]
+    rng_f = np.random.Generator(np.random.PCG64(SEED + 9))
+    z = {"raw": raw2, "n_img": np.asarray([len(runs)], np.int32)}
+    first_cam = {}
+    for k, (cam, scale) in enumerate(runs):
+        opt = dict(depth_image_scale=scale, max_proj_scale=10, min_proj_scale=2, min_proj_dist=2.0, submap_length=1.0, submap_width=1.0,
+                   submap_height=1.0, choose_meter=40.0, min_lidar_proj_dist=0.5)
+        if scale not in first_cam:
+            first_cam[scale] = cam["cam"]                 # the function-local statics are set by the first camera of a run
+        coef = pn.splat_coef(first_cam[scale], opt)
+        w, h = cam["width"], cam["height"]
+        dense = pn.project(world2, cam["qvec"], cam["tvec"], cam["cam"], w, h, opt, coef)
+        assert np.array_equal(dense["first"], dense["lowest"]), "tie between cells: first-visited != lowest index"
+        feat = np.stack([rng_f.uniform(-5, w + 5, 400), rng_f.uniform(-5, h + 5, 400)], 1)
+        fpix = pn.feature_pixels(feat, scale, w, h)
+        mask = np.zeros(dense["range"].size, dtype=bool)
+        mask[fpix[fpix >= 0]] = True
+        fw = pn.project(world2, cam["qvec"], cam["tvec"], cam["cam"], w, h, opt, coef, feat_mask=mask)
+        assert np.array_equal(fw["first"], fw["lowest"])
+        win = np.where(fpix >= 0, fw["lowest"].reshape(-1)[np.maximum(fpix, 0)], -1)
+        packed = dense["packed_lowest"].reshape(-1)
+        pix = np.nonzero(packed != np.iinfo(np.uint64).max)[0].astype(np.int32)
         z[f"img{k}_qvec"] = np.asarray(cam["qvec"], np.float64)
         z[f"img{k}_tvec"] = np.asarray(cam["tvec"], np.float64)
         z[f"img{k}_cam"] = np.asarray(cam["cam"], np.float64)
-        z[f"img{k}_wh"] = np.asarray([cam["width"], cam["height"]], np.int32)
-        flat = zb.reshape(-1)
-        pix = np.nonzero(flat != np.iinfo(np.uint64).max)[0].astype(np.int32)
+        z[f"img{k}_wh"] = np.asarray([w, h], np.int32)
+        z[f"img{k}_scale"] = np.asarray([scale], np.float64)
+        z[f"img{k}_coef"] = coef
+        z[f"img{k}_shape"] = np.asarray(dense["range"].shape, np.int32)
+        z[f"img{k}_nsel"] = np.asarray([dense["n_sel"]], np.int64)
         z[f"img{k}_covered"] = np.asarray([len(pix)], np.int64)
-        z[f"img{k}_sha256"] = np.frombuffer(hashlib.sha256(flat.tobytes()).digest(), np.uint8)   # whole buffer
-        pix = pix[:: max(1, len(pix) // 4000)]               # plus a readable sample of packed winners
-        z[f"img{k}_pix"] = pix
-        z[f"img{k}_val"] = flat[pix]
-        z[f"img{k}_shape"] = np.asarray(zb.shape, np.int32)
-    z["raw"] = raw2
-    z["coef"] = np.asarray(coef, np.float64)
+        z[f"img{k}_sha256"] = np.frombuffer(hashlib.sha256(packed.tobytes()).digest(), np.uint8)   # whole packed buffer
+        samp = pix[:: max(1, len(pix) // 4000)]
+        z[f"img{k}_pix"] = samp
+        z[f"img{k}_val"] = packed[samp]
+        z[f"img{k}_feat"] = feat
+        z[f"img{k}_feat_pix"] = fpix
+        z[f"img{k}_feat_win"] = win.astype(np.int64)
+        print(f"zbuf img{k}: scale {scale}, {dense['n_sel']} cells, {len(pix)} covered pixels, {int((win >= 0).sum())} feature winners")
+    # the hand-placed points must have done what they were placed for (identity-pose image = run 2)
+    n0 = len(world2) - 5
+    d2 = pn.project(world2[n0:], ident["qvec"], ident["tvec"], ident["cam"], 1920, 1080,
+                    dict(depth_image_scale=1.0, max_proj_scale=10, min_proj_scale=2, min_proj_dist=2.0, submap_length=1.0, submap_width=1.0,
+                         submap_height=1.0, choose_meter=40.0, min_lidar_proj_dist=0.5), z["img2_coef"])
+    won = set(np.unique(d2["lowest"][d2["lowest"] >= 0]).tolist())
+    assert won == {0, 1, 4}, won                          # the too-near and the behind-the-camera points project nothing
     np.savez_compressed(os.path.join(HERE, "zbuf_small.npz"), **z)
-    print("zbuf_small.npz:", len(world2), "points, 3 images,", sum(int(z[f"img{k}_covered"][0]) for k in range(3)), "covered pixels")
 
 
 if __name__ == "__main__":

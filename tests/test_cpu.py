@@ -258,6 +258,12 @@ def test_resjac_nan_at_zero(orc):
     assert r[0] == 0.0 and np.isnan(J).all()             # autodiff gives 0 * inf
 
 
+def test_resjac_nan_plane_adds_no_block(orc):
+    # AddLidarToProblem returns before Create when a plane coefficient is NaN (src/optim/bundle_adjustment.cc:1003-1007)
+    r, J = orc.resjac([[1.0, 2.0, 3.0], [1.0, 2.0, 3.0]], [[np.nan, 0.0, 1.0, -1.0], [0.0, 0.0, 1.0, np.nan]], [10.0, 10.0])
+    assert not r.any() and not J.any()
+
+
 def test_known_answer_vectors(orc):
     # hand-computed known answers (the reference has none for this path)
     r, J = orc.resjac([[1.0, 2.0, 3.0]], [[0.0, 0.0, 1.0, -1.0]], [10.0])

@@ -107,6 +107,54 @@ def test_nn_edge_cases(scene, pcd, ctx, orc):
     assert np.array_equal(a, b[:100])
 
 
+def test_nn_radius_boundary_at_map_scale(pcd, ctx, orc):
+    """The accept test is the reference's fp64 |l - p| <= R on the DOUBLE query; the search works on the float cast,
+    which moves a query by up to ~7e-6 m at 100 m coordinates.  Radii placed one fp64 ulp either side of the true
+    distance must still decide by that test (the float ball has to cover the cast displacement)."""
+    rng = np.random.default_rng(11)
+    off = np.array([412.7, -233.1, 167.9])
+    pts = (rng.uniform(-4, 4, (30_000, 3)) + off).astype(np.float32)
+    cloud = np.zeros((len(pts), 8), np.float32); cloud[:, :3] = pts; cloud[:, 5] = -1.0
+    cl = pcd.Cloud(ctx, cloud); cl.build_index()
+    q = rng.uniform(-3.5, 3.5, (6000, 3)) + off
+    bi, _ = orc.nn_brute(cloud, q)
+    l = pts[bi].astype(np.float64)
+    v = l - q
+    dist = np.sqrt(v[:, 0] * v[:, 0] + (v[:, 1] * v[:, 1] + v[:, 2] * v[:, 2]))      # Eigen's (l - p).norm()
+    for radius, hit in ((dist, True), (np.nextafter(dist, np.inf), True), (np.nextafter(dist, -np.inf), False)):
+        idx, _ = cl.nn(q, radius)
+        assert np.array_equal(idx >= 0, np.full(len(q), hit)), (hit, int((idx >= 0).sum()))
+        if hit:
+            assert np.array_equal(idx, bi)
+    cl.close()
+
+
+def test_fused_pass_nan_plane_adds_no_block(pcd, ctx, orc):
+    """An infinite normal survives the NaN / zero-normal test of ply.cc:100-101, normalises to NaN coefficients and is
+    stored as a match, but AddLidarToProblem (bundle_adjustment.cc:1003-1007) adds no residual block for it."""
+    rng = np.random.default_rng(3)
+    pts = rng.uniform(-2, 2, (5000, 3)).astype(np.float32)
+    cloud = np.zeros((len(pts), 8), np.float32); cloud[:, :3] = pts; cloud[:, 5] = -1.0
+    cloud[::7, 4] = np.inf                                      # every 7th point: normal (inf, -1, 0)
+    cl = pcd.Cloud(ctx, cloud); cl.build_index()
+    q = pts[:3000].astype(np.float64) + rng.normal(0, 0.01, (3000, 3))
+    W = (10.0, 1000.0, 10000.0)
+    rec, r, J, s = cl.associate_evaluate(q, W, range_=np.full(len(q), 0.5), variant=pcd.ASSOC_GLOBAL)
+    tree = orc.KdTree(cloud)
+    want = tree.associate(q, np.full(len(q), 0.5), variant=1)
+    acc = want["accepted"].astype(bool)
+    assert np.array_equal(rec["accepted"].astype(bool), acc)
+    bad = acc & np.isnan(want["abcd"]).any(axis=1)
+    assert bad.sum() > 100 and np.array_equal(np.isnan(rec["abcd"]).any(axis=1)[acc], np.isnan(want["abcd"]).any(axis=1)[acc])
+    assert not r[bad].any() and not J[bad].any() and np.isfinite(s)
+    w = np.where(want["type"] == 2, W[2], W[1])
+    ro, Jo = orc.resjac(q[acc], want["abcd"][acc], w[acc])
+    assert _close(r[acc], ro) and _close(J[acc], Jo) and _close(s, float(np.sum(ro * ro)), 1e-9)
+    r3, J3, s3 = ctx.residual_jacobian(q[acc], rec["abcd"][acc], w[acc])            # the standalone kernel: same rule
+    assert np.array_equal(r3, r[acc]) and np.array_equal(J3, J[acc], equal_nan=True)
+    cl.close()
+
+
 def test_nn_ties_lowest_index(pcd, ctx, orc):
     # duplicated and mirrored points: exact float ties must resolve to the lowest index
     rng = np.random.default_rng(5)
