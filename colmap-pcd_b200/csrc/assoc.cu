@@ -189,6 +189,28 @@ __global__ void k_match_proj(const double* __restrict__ p, const double* __restr
   if (angle_out) angle_out[i] = ang;
 }
 
+// The arithmetic of the match record as the reference's class methods expose it (src/lidar/lidar_point.cc:21-50):
+// Normalize, ComputeDist, ComputePointToPointDist, ComputeAngle, same device functions as k_assoc_record.  The shim's
+// colmap::LidarPoint calls this with n = 1 where a call site is left serial; batched callers never need it.
+__global__ void k_lidar_point_ops(const double* __restrict__ xyz, const double* __restrict__ abcd_in, const double* __restrict__ pt, int64_t n,
+                                  int normalize, double* __restrict__ abcd_out, double* __restrict__ d_plane, double* __restrict__ d_point,
+                                  double* __restrict__ angle) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double l[6] = {xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], abcd_in[4 * i], abcd_in[4 * i + 1], abcd_in[4 * i + 2]};
+  double pl[4] = {abcd_in[4 * i], abcd_in[4 * i + 1], abcd_in[4 * i + 2], abcd_in[4 * i + 3]};
+  if (normalize) normalize_plane(l, pl);
+  if (abcd_out) { abcd_out[4 * i] = pl[0]; abcd_out[4 * i + 1] = pl[1]; abcd_out[4 * i + 2] = pl[2]; abcd_out[4 * i + 3] = pl[3]; }
+  if (!pt) return;
+  const double px = pt[3 * i], py = pt[3 * i + 1], pz = pt[3 * i + 2];
+  if (d_plane) d_plane[i] = fabs((px * pl[0] + (py * pl[1] + pz * pl[2])) + pl[3]);                 // ComputeDist
+  if (d_point) d_point[i] = norm3(l[0] - px, l[1] - py, l[2] - pz);                                 // ComputePointToPointDist
+  if (angle) {
+    const double wx = px - l[0], wy = py - l[1], wz = pz - l[2];
+    angle[i] = fabs((pl[0] * wx + (pl[1] * wy + pl[2] * wz)) / norm3(wx, wy, wz));                  // ComputeAngle
+  }
+}
+
 __global__ void k_sum_blocks(const double* __restrict__ partial, int nb, double* __restrict__ out) {
   __shared__ double sh[256];
   double s = 0.0;
@@ -387,6 +409,31 @@ int pcd_search_nn_batch(pcd_cloud* cloud, const double* q, int64_t n, double* l_
   PCD_LAUNCH_CHECK(ctx);
   PCD_CUDA(ctx, cudaMemcpyAsync(l_pt, d_l, 48 * (size_t)n, cudaMemcpyDeviceToHost, st));
   PCD_CUDA(ctx, cudaMemcpyAsync(ok, d_ok, (size_t)n, cudaMemcpyDeviceToHost, st));
+  PCD_CUDA(ctx, cudaStreamSynchronize(st));
+  return PCD_OK;
+}
+
+int pcd_lidar_point_ops(pcd_ctx* ctx, const double* xyz, const double* abcd, const double* pt, int64_t n, int normalize,
+                        double* abcd_out, double* dist_plane, double* dist_point, double* angle) {
+  if (!ctx || n < 0 || (n > 0 && (!xyz || !abcd))) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_lidar_point_ops: bad argument");
+  if (n == 0) return PCD_OK;
+  DeviceGuard g(ctx->device);
+  cudaStream_t st = ctx->stream;
+  PCD_CUDA(ctx, ctx->stage_in[0].ensure(80 * (size_t)n + 64));
+  PCD_CUDA(ctx, ctx->stage_out[0].ensure(56 * (size_t)n + 64));
+  double* d_xyz = ctx->stage_in[0].as<double>();
+  double* d_abcd = d_xyz + 3 * n; double* d_pt = pt ? d_abcd + 4 * n : nullptr;
+  double* d_out = ctx->stage_out[0].as<double>();
+  double* d_dp = d_out + 4 * n; double* d_dd = d_dp + n; double* d_an = d_dd + n;
+  PCD_CUDA(ctx, cudaMemcpyAsync(d_xyz, xyz, 24 * (size_t)n, cudaMemcpyHostToDevice, st));
+  PCD_CUDA(ctx, cudaMemcpyAsync(d_abcd, abcd, 32 * (size_t)n, cudaMemcpyHostToDevice, st));
+  if (pt) PCD_CUDA(ctx, cudaMemcpyAsync(d_pt, pt, 24 * (size_t)n, cudaMemcpyHostToDevice, st));
+  pcd::k_lidar_point_ops<<<pcd_blocks(n, 128), 128, 0, st>>>(d_xyz, d_abcd, d_pt, n, normalize, d_out, d_dp, d_dd, d_an);
+  PCD_LAUNCH_CHECK(ctx);
+  if (abcd_out) PCD_CUDA(ctx, cudaMemcpyAsync(abcd_out, d_out, 32 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  if (pt && dist_plane) PCD_CUDA(ctx, cudaMemcpyAsync(dist_plane, d_dp, 8 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  if (pt && dist_point) PCD_CUDA(ctx, cudaMemcpyAsync(dist_point, d_dd, 8 * (size_t)n, cudaMemcpyDeviceToHost, st));
+  if (pt && angle) PCD_CUDA(ctx, cudaMemcpyAsync(angle, d_an, 8 * (size_t)n, cudaMemcpyDeviceToHost, st));
   PCD_CUDA(ctx, cudaStreamSynchronize(st));
   return PCD_OK;
 }

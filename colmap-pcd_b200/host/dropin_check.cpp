@@ -42,6 +42,125 @@ static std::vector<double> read_f64(const char* path) {
   return v;
 }
 
+// ---- the reference's three serial association loop bodies, transcribed: only the surrounding containers
+// (Reconstruction, BundleAdjustmentConfig) are replaced by a std::map; every statement that touches
+// PointCloudProcess, Eigen or colmap::LidarPoint is the reference's own text.
+// src/optim/bundle_adjustment.cc:358-410 (MatchClosestLidarPoint, local BA)
+static void LoopLocal(lidar::PointCloudProcess* point_cloud_process_, uint64_t point3D_id, Eigen::Vector3d pt_xyz,
+                      double& max_search_range, std::map<uint64_t, LidarPoint>& lidar_maps_) {
+  Eigen::Vector6d lidar_pt;
+  if (point_cloud_process_->SearchNearestNeiborByKdtree(pt_xyz,lidar_pt)){
+    Eigen::Vector3d norm = lidar_pt.block(3,0,3,1);
+    Eigen::Vector3d l_pt = lidar_pt.block(0,0,3,1);
+    double d = 0 - l_pt.dot(norm);
+    Eigen::Vector4d plane;
+    plane << norm(0),norm(1),norm(2),d;
+
+    LidarPoint lidar_point(l_pt,plane);
+    if (std::abs(norm(1)/norm(0))>10 && std::abs(norm(1)/norm(2))>10) {
+      lidar_point.SetType(LidarPointType::IcpGround);
+      Eigen::Vector3ub color;
+      color << 255,255,0;
+      lidar_point.SetColor(color);
+    } else {
+      lidar_point.SetType(LidarPointType::Icp);
+      Eigen::Vector3ub color;
+      color << 0,255,0;
+      lidar_point.SetColor(color);
+    }
+
+    double dist = lidar_point.ComputePointToPointDist(pt_xyz);
+    if (dist > max_search_range) return;
+
+    lidar_point.SetDist(dist);
+    lidar_point.SetAngle( lidar_point.ComputeAngle(pt_xyz));
+
+    lidar_maps_.insert({point3D_id,lidar_point});
+  }
+}
+// src/sfm/incremental_mapper.cc:1432-1466 (global BA by lidar)
+static void LoopGlobal(lidar::PointCloudProcess* lidar_pointcloud_process_, uint64_t point3D_id, Eigen::Vector3d pt_xyz,
+                       double max_search_range, std::map<uint64_t, LidarPoint>& lidar_maps_) {
+      Eigen::Vector6d lidar_pt;
+      if (lidar_pointcloud_process_->SearchNearestNeiborByKdtree(pt_xyz,lidar_pt)) {
+        Eigen::Vector3d norm = lidar_pt.block(3,0,3,1);
+        Eigen::Vector3d l_pt = lidar_pt.block(0,0,3,1);
+
+        double d = 0 - l_pt.dot(norm);
+        Eigen::Vector4d plane;
+        plane << norm(0),norm(1),norm(2),d;
+
+        LidarPoint lidar_point(l_pt,plane);
+
+        if (std::abs(norm(1)/norm(0))>10 && std::abs(norm(1)/norm(2))>10) {
+          lidar_point.SetType(LidarPointType::IcpGround);
+          Eigen::Vector3ub color;
+          color << 255,255,0;
+          lidar_point.SetColor(color);
+        } else {
+          lidar_point.SetType(LidarPointType::Icp);
+          Eigen::Vector3ub color;
+          color << 0,0,255;
+          lidar_point.SetColor(color);
+        }
+
+        double dist = lidar_point.ComputePointToPointDist(pt_xyz);
+        if (dist > max_search_range) return;
+
+        lidar_maps_.insert({point3D_id,lidar_point});
+      }
+}
+// src/controllers/bundle_adjustment.cc:142-183 (whole-map refine)
+static void LoopWholeMap(lidar::PointCloudProcess* lidar_pointcloud_process_, uint64_t point3d_id, Eigen::Vector3d pt_xyz,
+                         std::map<uint64_t, LidarPoint>& lidar_maps_) {
+      Eigen::Vector6d lidar_pt;
+      if (lidar_pointcloud_process_->SearchNearestNeiborByKdtree(pt_xyz,lidar_pt)){
+        Eigen::Vector3d norm = lidar_pt.block(3,0,3,1);
+        Eigen::Vector3d l_pt = lidar_pt.block(0,0,3,1);
+
+        double d = 0 - l_pt.dot(norm);
+        Eigen::Vector4d plane;
+        plane << norm(0),norm(1),norm(2),d;
+
+        LidarPoint lidar_point(l_pt,plane);
+
+        const double dist2plane = lidar_point.ComputeDist(pt_xyz);
+        const double dist2point = lidar_point.ComputePointToPointDist(pt_xyz);
+
+        if (dist2plane > 1 || dist2point > 2) return;
+
+        if (std::abs(norm(1)/norm(0))>10 && std::abs(norm(1)/norm(2))>10) {
+          lidar_point.SetType(LidarPointType::IcpGround);
+          Eigen::Vector3ub color;
+          color << 255,255,0;
+          lidar_point.SetColor(color);
+        } else {
+          lidar_point.SetType(LidarPointType::Icp);
+          Eigen::Vector3ub color;
+          color << 0,0,255;
+          lidar_point.SetColor(color);
+        }
+
+        lidar_maps_.insert({point3d_id,lidar_point});
+      }
+}
+
+// serial loop vs batched MatchClosestLidarPoints on the same points: same ids, bit-identical records
+static bool SameRecords(std::map<uint64_t, LidarPoint>& a, std::map<uint64_t, LidarPoint>& b, bool with_dist_angle, const char* what) {
+  if (a.size() != b.size()) { fprintf(stderr, "%s: %zu serial vs %zu batched matches\n", what, a.size(), b.size()); return false; }
+  for (auto& kv : a) {
+    auto it = b.find(kv.first);
+    if (it == b.end()) { fprintf(stderr, "%s: id %llu missing\n", what, (unsigned long long)kv.first); return false; }
+    LidarPoint &x = kv.second, &y = it->second;
+    bool ok = x.Type() == y.Type();
+    for (int c = 0; c < 3; c++) ok = ok && x.LidarXYZ()(c) == y.LidarXYZ()(c) && x.Color()(c) == y.Color()(c);
+    for (int c = 0; c < 4; c++) ok = ok && (x.LidarABCD()(c) == y.LidarABCD()(c) || (x.LidarABCD()(c) != x.LidarABCD()(c) && y.LidarABCD()(c) != y.LidarABCD()(c)));
+    if (with_dist_angle) ok = ok && x.Dist() == y.Dist() && (x.Angle() == y.Angle() || (x.Angle() != x.Angle() && y.Angle() != y.Angle()));
+    if (!ok) { fprintf(stderr, "%s: record of id %llu differs\n", what, (unsigned long long)kv.first); return false; }
+  }
+  return true;
+}
+
 int main(int argc, char** argv) {
   if (argc < 4) { fprintf(stderr, "usage: dropin_check cloud.ply queries.f64 out.f64 [image.f64]\n"); return 2; }
   lidar::PcdProjectionOptions opt;
@@ -78,21 +197,69 @@ int main(int argc, char** argv) {
   std::map<uint64_t, LidarPoint> matches;
   if (!MatchClosestLidarPoints(pcp, ids, xyz, on, 1.5, 0.2, 0.1, PCD_ASSOC_GLOBAL, &matches)) { fprintf(stderr, "batch association failed\n"); return 1; }
   out.push_back((double)matches.size());
-  LidarEvaluationBatch::Reset();
+  {
+    // (2b) the reference's own serial loop bodies over the shim == the batched calls, for all three variants
+    const int64_t m = n < 400 ? n : 400;
+    std::vector<uint64_t> ids_m(ids.begin(), ids.begin() + m); std::vector<double> xyz_m(xyz.begin(), xyz.begin() + 3 * m);
+    std::vector<int32_t> on_m(on.begin(), on.begin() + m);
+    std::map<uint64_t, LidarPoint> sl, sg, sw, bl, bg, bw;
+    for (int64_t i = 0; i < m; i++) {
+      Eigen::Vector3d p{xyz_m[3 * i], xyz_m[3 * i + 1], xyz_m[3 * i + 2]};
+      double range = 1.5 - on_m[i] * 0.1;                                  // src/sfm/incremental_mapper.cc:1159-1163
+      if (range <= 0.2) range = 0.2;
+      LoopLocal(&pcp, ids_m[i], p, range, sl);
+      LoopGlobal(&pcp, ids_m[i], p, range, sg);
+      LoopWholeMap(&pcp, ids_m[i], p, sw);
+    }
+    if (!MatchClosestLidarPoints(pcp, ids_m, xyz_m, on_m, 1.5, 0.2, 0.1, PCD_ASSOC_LOCAL, &bl) ||
+        !MatchClosestLidarPoints(pcp, ids_m, xyz_m, on_m, 1.5, 0.2, 0.1, PCD_ASSOC_GLOBAL, &bg) ||
+        !MatchClosestLidarPoints(pcp, ids_m, xyz_m, on_m, 1.5, 0.2, 0.1, PCD_ASSOC_WHOLE_MAP, &bw)) { fprintf(stderr, "batched variants failed\n"); return 1; }
+    if (!SameRecords(sl, bl, true, "local loop") || !SameRecords(sg, bg, false, "global loop") || !SameRecords(sw, bw, false, "whole-map loop")) return 1;
+    if (sl.size() < 100) { fprintf(stderr, "too few matches to mean anything (%zu)\n", sl.size()); return 1; }
+    // Reconstruction::FilterLidarOutlier's test (src/base/reconstruction.cc:783-800) on the stored records, moved points
+    size_t num_filtered = 0, expect = 0;
+    for (auto& kv : sg) {
+      LidarPoint l_pt = kv.second;
+      const int64_t i = (int64_t)(kv.first - 1000);
+      Eigen::Vector3d i_pt_xyz{xyz_m[3 * i] + 0.05 * (double)(i % 7), xyz_m[3 * i + 1], xyz_m[3 * i + 2]};
+      double dist = l_pt.ComputePointToPointDist(i_pt_xyz);
+      if (l_pt.Type() == LidarPointType::Proj){
+        if (dist > 0.2) num_filtered += 1;
+      } else {
+        if (dist > 0.25) num_filtered += 1;
+      }
+      double lx[3] = {l_pt.LidarXYZ()(0), l_pt.LidarXYZ()(1), l_pt.LidarXYZ()(2)}; uint8_t ty = PCD_TYPE_ICP, er = 0; int64_t cnt = 0;
+      if (pcd_filter_outliers_batch(lidar::DropinRuntime::Get().ctx, i_pt_xyz.data(), lx, &ty, 1, 0.2, 0.25, &er, &cnt) != PCD_OK) return 1;
+      expect += er;
+    }
+    if (num_filtered != expect || num_filtered == 0) { fprintf(stderr, "FilterLidarOutlier: serial %zu vs batched %zu\n", num_filtered, expect); return 1; }
+  }
+  std::shared_ptr<LidarEvaluationBatch> batch = LidarEvaluationBatch::Begin();     // one batch per ceres::Problem
   std::vector<ceres::CostFunction*> fns; std::vector<const double*> blocks;
   for (auto& kv : matches) {
     LidarPoint& lp = kv.second;
     const double w = lp.Type() == LidarPointType::IcpGround ? 10000.0 : (lp.Type() == LidarPointType::Icp ? 1000.0 : 10.0);
     ceres::CostFunction* f = BundleAdjustmentLidarCostFunction::Create(lp.LidarABCD(), w);     // bundle_adjustment.cc:1032
     const double* block = &xyz[3 * (kv.first - 1000)];
-    LidarEvaluationBatch::Current()->SetPointPtr(static_cast<BundleAdjustmentLidarCostFunction*>(f)->slot(), block);
+    batch->SetPointPtr(static_cast<BundleAdjustmentLidarCostFunction*>(f)->slot(), block);     // the pointer given to AddResidualBlock (:1037)
     fns.push_back(f); blocks.push_back(block);
   }
-  LidarEvaluationCallback cb;
+  {
+    // a batch with an unbound slot refuses to prepare instead of reading through a stale pointer
+    std::shared_ptr<LidarEvaluationBatch> other = LidarEvaluationBatch::Begin();
+    Eigen::Vector4d pl{0.0, 0.0, 1.0, -1.0};
+    ceres::CostFunction* g = BundleAdjustmentLidarCostFunction::Create(pl, 10.0);
+    if (other->Prepare(true)) { fprintf(stderr, "unbound slot was prepared\n"); return 1; }
+    delete g;
+  }
+  LidarEvaluationCallback cb(batch);
   cb.PrepareForEvaluation(true, true);
   size_t k = 0;
   for (auto& kv : matches) {
-    double r = 0, J[3] = {0, 0, 0}; double* jac[1] = {J}; const double* par[1] = {blocks[k]};
+    // Ceres hands Evaluate its own state vector, never the block's storage: a COPY of the values must be served from
+    // the prepared batch and must not rebind anything
+    double r = 0, J[3] = {0, 0, 0}; double* jac[1] = {J};
+    const double state[3] = {blocks[k][0], blocks[k][1], blocks[k][2]}; const double* par[1] = {state};
     if (!fns[k]->Evaluate(par, &r, jac)) { fprintf(stderr, "Evaluate failed\n"); return 1; }
     LidarPoint& lp = kv.second;
     out.push_back((double)kv.first); out.push_back((double)(int)lp.Type());
@@ -108,6 +275,14 @@ int main(int argc, char** argv) {
     double r = -1, J[3]; double* jac[1] = {J};
     if (!fns[0]->Evaluate(par, &r, jac)) { fprintf(stderr, "unprepared Evaluate failed\n"); return 1; }
     out.push_back(r);
+    // ... and the probe left the batch bound to the blocks: the next iteration still prepares from the user's storage
+    xyz[3 * (matches.begin()->first - 1000)] += 0.25;
+    cb.PrepareForEvaluation(true, true);
+    const double* par2[1] = {blocks[0]};
+    double r2 = -1;
+    if (!fns[0]->Evaluate(par2, &r2, jac) || !batch->Matches(0, blocks[0])) { fprintf(stderr, "batch lost its binding\n"); return 1; }
+    out.push_back(r2);
+    xyz[3 * (matches.begin()->first - 1000)] -= 0.25;
   }
   for (auto* f : fns) delete f;
   // (3) depth projection through PcdProj::SetNewImage (map overload), optional
@@ -135,6 +310,14 @@ int main(int argc, char** argv) {
       return true;
     };
     if (cache.size() != 2 || !same(cache[7], m) || !same(cache[9], m2)) { fprintf(stderr, "batched SetNewImages differs from SetNewImage\n"); return 1; }
+    // (4) the initial-pair overload (src/lidar/pcd_projection.cc:102-220): one push_back per keypoint after what the vector held
+    std::vector<std::pair<Eigen::Vector2d, bool>> pt_xys;
+    for (int64_t i = 0; i < nf; i++) pt_xys.push_back({Eigen::Vector2d{im[18 + 2 * i], im[19 + 2 * i]}, false});
+    std::vector<Eigen::Vector3d> pt_xyzs(1, Eigen::Vector3d{7.0, 7.0, 7.0});
+    pcp.pcd_proj_->SetNewImage(image, cam, pt_xys, pt_xyzs);
+    if (pt_xyzs.size() != (size_t)nf + 1 || pt_xyzs[0](0) != 7.0) { fprintf(stderr, "init SetNewImage must append one entry per keypoint\n"); return 1; }
+    out.push_back((double)nf);
+    for (int64_t i = 0; i < nf; i++) { out.push_back(pt_xys[i].second ? 1.0 : 0.0); for (int c = 0; c < 3; c++) out.push_back(pt_xyzs[i + 1](c)); }
   }
   FILE* f = fopen(argv[3], "wb");
   if (!f || fwrite(out.data(), 8, out.size(), f) != out.size()) return 1;

@@ -44,6 +44,14 @@ template <typename T, int N> struct PcdVec {
   const T& operator[](int i) const { return v[i]; }
   T* data() { return v; }
   const T* data() const { return v; }
+  // the few Eigen operations the reference's association loops spell out (block(i,0,3,1), a.dot(b), v << a,b,c,d)
+  PcdVec<T, 3> block(int i, int, int, int) const { PcdVec<T, 3> r; for (int k = 0; k < 3; k++) r.v[k] = v[i + k]; return r; }
+  T dot(const PcdVec& o) const { T s = T(0); for (int k = 0; k < N; k++) s += v[k] * o.v[k]; return s; }
+  struct Comma {
+    PcdVec* m; int i;
+    Comma operator,(T x) { if (i < N) m->v[i] = x; return Comma{m, i + 1}; }
+  };
+  Comma operator<<(T x) { v[0] = x; return Comma{this, 1}; }
 };
 using Vector2d = PcdVec<double, 2>;
 using Vector3d = PcdVec<double, 3>;
@@ -117,6 +125,14 @@ struct DropinRuntime {
     return true;
   }
   ~DropinRuntime() { if (ctx) pcd_ctx_destroy(ctx); }
+  // A context of the calling thread's own (streams and scratch are per context), for the small per-record calls a
+  // serial call site or a Ceres worker thread makes: no process-wide lock is taken on that path.
+  static pcd_ctx* Thread() {
+    struct Holder { pcd_ctx* c = nullptr; ~Holder() { if (c) pcd_ctx_destroy(c); } };
+    static thread_local Holder h;
+    if (!h.c && pcd_ctx_create(0, &h.c) != PCD_OK) h.c = nullptr;
+    return h.c;
+  }
 };
 
 // Device-resident cloud shared between Kdtree and PcdProj (the reference keeps three host copies).
@@ -299,10 +315,11 @@ class PcdProj {                      // src/lidar/pcd_projection.h:49-66
         rt.error = pcd_last_error(rt.ctx); return;
       }
     }
-    pt_xyzs.resize(n);
-    for (size_t k = 0; k < n; k++) {
+    for (size_t k = 0; k < n; k++) {                       // one push_back per keypoint, zero vector when unmatched (:147-205)
       pt_xys[k].second = matched[k] != 0;
-      pt_xyzs[k](0) = xyz[3 * k]; pt_xyzs[k](1) = xyz[3 * k + 1]; pt_xyzs[k](2) = xyz[3 * k + 2];
+      typename XYZs::value_type v;
+      v(0) = xyz[3 * k]; v(1) = xyz[3 * k + 1]; v(2) = xyz[3 * k + 2];
+      pt_xyzs.push_back(v);
     }
   }
   pcd_cloud* handle() const { return dev_ ? dev_->h : nullptr; }
@@ -410,13 +427,21 @@ class PointCloudProcess {            // src/lidar/ply.h:13-40
 // ---------------------------------------------------------------------------------------------
 enum class LidarPointType { Proj, Icp, IcpGround };       // src/lidar/lidar_point.h:9
 
-// The match record (src/lidar/lidar_point.h:10-52).  Plain storage: every field is produced by the
-// batched association kernel (pcd_associate_batch) and installed with FromBatch(); the record does
-// no arithmetic of its own.
+// The match record (src/lidar/lidar_point.h:10-52), full interface.  Records produced by the batched association
+// (pcd_associate_batch) are installed with FromBatch() and carry every field already.  The constructors and the
+// Compute* methods exist for call sites that stay serial (src/optim/bundle_adjustment.cc:368-408,
+// src/sfm/incremental_mapper.cc:1432-1466, src/controllers/bundle_adjustment.cc:142-183, src/base/reconstruction.cc:787):
+// like the reference both constructors Normalize(); the arithmetic runs in pcd_lidar_point_ops (one record per call, on
+// the calling thread's own context), the same device code the batched record kernel uses, so serial and batched
+// results are bit-identical.  (Inside the reference tree the class of src/lidar/lidar_point.{h,cc} -- no PCL in it -- may
+// simply be kept: define PCD_DROPIN_KEEP_LIDAR_POINT and include it before this header.)
+#ifndef PCD_DROPIN_KEEP_LIDAR_POINT
 class LidarPoint {
  public:
   LidarPoint() {}
-  LidarPoint(LidarPointType type, const Eigen::Vector3d& xyz, const Eigen::Vector4d& abcd) : type_(type), xyz_(xyz), abcd_(abcd) {}
+  LidarPoint(LidarPointType type, Eigen::Vector3d& xyz, Eigen::Vector4d& abcd) : type_(type), xyz_(xyz), abcd_(abcd) { Normalize(); }
+  LidarPoint(Eigen::Vector3d& xyz, Eigen::Vector4d& abcd) : xyz_(xyz), abcd_(abcd) { Normalize(); }
+  ~LidarPoint() {}
   static LidarPoint FromBatch(const pcd_assoc_out& o, int64_t i) {
     LidarPoint p;
     p.type_ = o.type[i] == PCD_TYPE_ICP_GROUND ? LidarPointType::IcpGround
@@ -429,22 +454,41 @@ class LidarPoint {
     return p;
   }
   void SetType(LidarPointType type) { type_ = type; }
-  void SetColor(const Eigen::Vector3ub& color) { color_ = color; }
+  void SetColor(Eigen::Vector3ub& color) { color_ = color; }
   void SetDist(const double& dist) { dist_ = dist; }
   void SetAngle(const double& angle) { angle_ = angle; }
-  Eigen::Vector3d LidarXYZ() const { return xyz_; }
-  Eigen::Vector4d LidarABCD() const { return abcd_; }
+  Eigen::Vector3d LidarXYZ() { return xyz_; }
+  const Eigen::Vector3d LidarXYZ() const { return xyz_; }
+  Eigen::Vector4d LidarABCD() { return abcd_; }
+  const Eigen::Vector4d LidarABCD() const { return abcd_; }
+  LidarPointType Type() { return type_; }
   LidarPointType Type() const { return type_; }
-  double Dist() const { return dist_; }
-  double Angle() const { return angle_; }
+  const double Dist() { return dist_; }
+  const double Angle() { return angle_; }
   const Eigen::Vector3ub& Color() const { return color_; }
+  Eigen::Vector3ub& Color() { return color_; }
+  const double ComputeDist(Eigen::Vector3d& pt) { double d = NaN(); Ops(&pt, 0, nullptr, &d, nullptr, nullptr); return d; }
+  const double ComputePointToPointDist(Eigen::Vector3d& pt) { double d = NaN(); Ops(&pt, 0, nullptr, nullptr, &d, nullptr); return d; }
+  const double ComputeAngle(Eigen::Vector3d& pt) { double a = NaN(); Ops(&pt, 0, nullptr, nullptr, nullptr, &a); return a; }
+  void Normalize() { double out[4]; if (Ops(nullptr, 1, out, nullptr, nullptr, nullptr)) for (int k = 0; k < 4; k++) abcd_(k) = out[k]; }
  private:
+  static double NaN() { return std::nan(""); }
+  // without a usable device the record keeps its fields / the methods return NaN: nothing is computed on the host
+  bool Ops(const Eigen::Vector3d* pt, int normalize, double* abcd_out, double* d_plane, double* d_point, double* angle) const {
+    pcd_ctx* c = lidar::DropinRuntime::Thread();
+    if (!c) return false;
+    const double xyz[3] = {xyz_(0), xyz_(1), xyz_(2)}, pl[4] = {abcd_(0), abcd_(1), abcd_(2), abcd_(3)};
+    double p[3] = {0, 0, 0};
+    if (pt) for (int k = 0; k < 3; k++) p[k] = (*pt)(k);
+    return pcd_lidar_point_ops(c, xyz, pl, pt ? p : nullptr, 1, normalize, abcd_out, d_plane, d_point, angle) == PCD_OK;
+  }
   LidarPointType type_ = LidarPointType::Icp;
   Eigen::Vector3d xyz_;
   Eigen::Vector4d abcd_;
   Eigen::Vector3ub color_;
   double dist_ = 0, angle_ = 0;
 };
+#endif
 
 // Batched replacement of the three serial association loops (src/sfm/incremental_mapper.cc:1138-1166,
 // :1411-1470; src/controllers/bundle_adjustment.cc:126-185).  ids / xyz: the variable points in the
@@ -474,10 +518,16 @@ inline bool MatchClosestLidarPoints(lidar::PointCloudProcess& pcp, const std::ve
 
 // ---------------------------------------------------------------------------------------------
 // Cost function + evaluation callback (src/base/cost_functions.h:180-232).
-// Every lidar cost function owns one slot of a LidarEvaluationBatch.  PrepareForEvaluation gathers the
-// current 3-D points, runs pcd_residual_jacobian_batch once on the GPU and fills r / J; Evaluate then
-// copies its slot (thread-safe, read-only).  A cost function evaluated without a prepared batch runs a
-// one-element batch on the GPU -- slower, never a host formula.
+// A LidarEvaluationBatch belongs to ONE ceres::Problem.  The bundle adjuster opens it before it adds residual blocks
+// (LidarEvaluationBatch::Begin(), which makes it the calling thread's current batch), every cost function created by
+// Create() takes a slot in it, the caller binds the slot to the point's own storage (SetPointPtr -- the same pointer it
+// hands to AddResidualBlock, src/optim/bundle_adjustment.cc:1037) and installs a LidarEvaluationCallback(batch) in
+// Problem::Options.  PrepareForEvaluation gathers the current points from those pointers (Ceres has copied its state
+// into them), runs pcd_residual_jacobian_batch once and fills r / J; Evaluate() is then a read-only copy of its slot,
+// safe from any number of Ceres threads.  The pointer Ceres passes to Evaluate() is its own state vector, not the
+// block's storage, so Evaluate() never records it: it only compares VALUES with the prepared point.  An evaluation
+// at another point (no callback installed, a probe between Prepare calls) is a one-element batch on the calling
+// thread's own context -- slower, lock-free, never a host formula.
 class LidarEvaluationBatch {
  public:
   int64_t Add(const double abcd[4], double weight, const double* point_ptr) {
@@ -490,8 +540,11 @@ class LidarEvaluationBatch {
   void SetPointPtr(int64_t slot, const double* p) { ptr_[(size_t)slot] = p; }
   bool Prepare(bool jacobians) {
     const int64_t n = (int64_t)w_.size();
-    for (int64_t i = 0; i < n; i++)
+    prepared_ = false;
+    for (int64_t i = 0; i < n; i++) {
+      if (!ptr_[i]) return false;                           // an unbound slot: the caller forgot SetPointPtr
       for (int k = 0; k < 3; k++) p_[3 * i + k] = ptr_[i][k];
+    }
     lidar::DropinRuntime& rt = lidar::DropinRuntime::Get();
     if (!rt.Ensure()) return false;
     std::lock_guard<std::mutex> g(rt.mu);
@@ -510,8 +563,11 @@ class LidarEvaluationBatch {
   double w(int64_t s) const { return w_[(size_t)s]; }
   double sum_sq() const { return sum_sq_; }
   int64_t size() const { return (int64_t)w_.size(); }
-  static std::shared_ptr<LidarEvaluationBatch>& Current() { static std::shared_ptr<LidarEvaluationBatch> b = std::make_shared<LidarEvaluationBatch>(); return b; }
-  static void Reset() { Current() = std::make_shared<LidarEvaluationBatch>(); }
+  // The batch new cost functions attach to (per thread: problems are built by one thread, src/optim/bundle_adjustment.cc:452-475).
+  static std::shared_ptr<LidarEvaluationBatch>& Current() { static thread_local std::shared_ptr<LidarEvaluationBatch> b; if (!b) b = std::make_shared<LidarEvaluationBatch>(); return b; }
+  // Opens the batch of the next problem; the previous one lives on for as long as its cost functions do.
+  static std::shared_ptr<LidarEvaluationBatch> Begin() { Current() = std::make_shared<LidarEvaluationBatch>(); return Current(); }
+  static void Reset() { Begin(); }
  private:
   std::vector<double> abcd_, w_, p_, r_, J_;
   std::vector<const double*> ptr_;
@@ -529,41 +585,43 @@ class LidarEvaluationCallback : public ceres::EvaluationCallback {
 
 class BundleAdjustmentLidarCostFunction : public ceres::CostFunction {
  public:
-  // cost_functions.h:180: same signature; ownership of the returned object passes to ceres::Problem.
+  // cost_functions.h:180: same signature; ownership of the returned object passes to ceres::Problem.  Bind the
+  // block's storage afterwards: batch->SetPointPtr(fn->slot(), point3D.XYZ().data()), or use the three-argument form.
   static ceres::CostFunction* Create(const Eigen::Matrix<double, 4, 1>& abcd, const double& weight) {
-    return new BundleAdjustmentLidarCostFunction(abcd, weight, LidarEvaluationBatch::Current());
+    return new BundleAdjustmentLidarCostFunction(abcd, weight, nullptr, LidarEvaluationBatch::Current());
+  }
+  static ceres::CostFunction* Create(const Eigen::Matrix<double, 4, 1>& abcd, const double& weight, const double* point_xyz) {
+    return new BundleAdjustmentLidarCostFunction(abcd, weight, point_xyz, LidarEvaluationBatch::Current());
   }
   bool Evaluate(double const* const* parameters, double* residuals, double** jacobians) const override {
     const double* p = parameters[0];
     const bool want_J = jacobians && jacobians[0];
-    if (slot_ptr_unset_) { batch_->SetPointPtr(slot_, p); slot_ptr_unset_ = false; }   // Ceres passes the block's own storage
-    if (batch_->Matches(slot_, p) && (!want_J || batch_->has_jacobians())) {
+    if (batch_->Matches(slot_, p) && (!want_J || batch_->has_jacobians())) {       // read-only
       residuals[0] = batch_->r(slot_);
       if (want_J) for (int k = 0; k < 3; k++) jacobians[0][k] = batch_->J(slot_)[k];
       return true;
     }
-    // not prepared for this point (no callback installed, or a line-search probe): one-element GPU batch
-    lidar::DropinRuntime& rt = lidar::DropinRuntime::Get();
-    if (!rt.Ensure()) return false;
-    std::lock_guard<std::mutex> g(rt.mu);
+    // not prepared for this point: one-element batch on this thread's own context
+    pcd_ctx* c = lidar::DropinRuntime::Thread();
+    if (!c) return false;
     double w = batch_->w(slot_), J[3];
-    if (pcd_residual_jacobian_batch(rt.ctx, p, batch_->abcd(slot_), &w, 1, residuals, want_J ? J : nullptr, nullptr) != PCD_OK) return false;
+    if (pcd_residual_jacobian_batch(c, p, batch_->abcd(slot_), &w, 1, residuals, want_J ? J : nullptr, nullptr) != PCD_OK) return false;
     if (want_J) for (int k = 0; k < 3; k++) jacobians[0][k] = J[k];
     return true;
   }
   int64_t slot() const { return slot_; }
+  const std::shared_ptr<LidarEvaluationBatch>& batch() const { return batch_; }
  private:
-  BundleAdjustmentLidarCostFunction(const Eigen::Matrix<double, 4, 1>& abcd, double weight, std::shared_ptr<LidarEvaluationBatch> b)
+  BundleAdjustmentLidarCostFunction(const Eigen::Matrix<double, 4, 1>& abcd, double weight, const double* point_xyz,
+                                    std::shared_ptr<LidarEvaluationBatch> b)
       : batch_(std::move(b)) {
     const double a[4] = {abcd(0), abcd(1), abcd(2), abcd(3)};
-    static const double zero[3] = {0, 0, 0};
-    slot_ = batch_->Add(a, weight, zero);
+    slot_ = batch_->Add(a, weight, point_xyz);
     set_num_residuals(1);
     mutable_parameter_block_sizes()->push_back(3);
   }
   std::shared_ptr<LidarEvaluationBatch> batch_;
   int64_t slot_ = 0;
-  mutable bool slot_ptr_unset_ = true;
 };
 
 }  // namespace colmap

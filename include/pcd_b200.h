@@ -183,6 +183,14 @@ PCD_API int pcd_associate_evaluate_batch_dev(pcd_cloud* cloud, const double* d_p
                                              double w_proj, double w_icp, double w_ground, const pcd_assoc_out* d_out,
                                              double* d_r, double* d_J, double* d_sum_sq, void* stream);
 
+/* The arithmetic of colmap::LidarPoint's own methods (src/lidar/lidar_point.h:12-13,37-41, lidar_point.cc:21-50) for n
+ * records: normalize != 0 applies Normalize() to (xyz, abcd) first (what both constructors do) and abcd_out receives the
+ * plane; with pt (3 doubles per record) given, dist_plane = ComputeDist(pt) = |pt . abc + d|, dist_point =
+ * ComputePointToPointDist(pt) = |xyz - pt|, angle = ComputeAngle(pt) = |abc . (pt - xyz)| / |pt - xyz| on that plane.
+ * Any output may be NULL.  The shim's colmap::LidarPoint calls this with n = 1 where a call site stays serial. */
+PCD_API int pcd_lidar_point_ops(pcd_ctx* ctx, const double* xyz, const double* abcd, const double* pt, int64_t n, int normalize,
+                                double* abcd_out, double* dist_plane, double* dist_point, double* angle);
+
 /* MatchVariablePoint2LidarPoint (src/optim/bundle_adjustment.cc:288-350): per point, among its
  * candidates cand[cand_start[i] .. cand_start[i+1]) (6 doubles each, track order) choose min
  * |v.n|/(|n||v|); outputs a Proj record (dist = point-to-plane).  found: uint8[n]. */

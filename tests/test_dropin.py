@@ -12,7 +12,9 @@ REL_TOL = 1e-5
 
 def _close(a, b, tol=REL_TOL):
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
-    return bool((np.abs(a - b) <= tol * np.maximum(np.abs(a), np.abs(b)) + 1e-300).all())
+    both_nan = np.isnan(a) & np.isnan(b)             # e.g. the ray/plane point of a zero normal: 0 / 0 on both sides
+    with np.errstate(invalid="ignore"):
+        return bool((both_nan | (np.abs(a - b) <= tol * np.maximum(np.abs(a), np.abs(b)) + 1e-300)).all())
 
 
 def test_shim_builds_and_fails_loudly_without_gpu(tmp_path):
@@ -69,6 +71,9 @@ def test_dropin_shim_matches_oracle(tmp_path, orc, synth, pcd):
     moved = q[acc[0]] + [0.5, 0, 0]
     rm, _ = orc.resjac([moved], want["abcd"][acc[:1]], wts[acc[:1]])
     assert _close(o[pos], rm[0]); pos += 1
+    # after the probe the batch is still bound to the blocks: the first block moved by 0.25, prepared again
+    rm2, _ = orc.resjac([q[acc[0]] + [0.25, 0, 0]], want["abcd"][acc[:1]], wts[acc[:1]])
+    assert _close(o[pos], rm2[0]); pos += 1
     # (3) PcdProj::SetNewImage (map overload) == oracle z-buffer winners at the feature pixels
     opt = orc.ProjOptions.default()
     sub = orc.Submap(world, opt)
@@ -88,3 +93,15 @@ def test_dropin_shim_matches_oracle(tmp_path, orc, synth, pcd):
     for row in got:
         gi = exp[int(row[0])]
         assert np.array_equal(row[1:4].astype(np.float32), world[gi, 0:3]) and np.array_equal(row[4:7].astype(np.float32), world[gi, 4:7])
+    pos += 7 * m
+    # (4) the initial-pair overload: matched flag and camera-frame point per keypoint (pcd_projection.cc:102-220)
+    nf = int(o[pos]); pos += 1
+    assert nf == len(feats)
+    init = o[pos:pos + 4 * nf].reshape(nf, 4); pos += 4 * nf
+    assert pos == len(o)
+    for k in range(nf):
+        assert bool(init[k, 0]) == (k in exp)
+        if k in exp:
+            assert _close(init[k, 1:4], orc.ray_plane(world, exp[k], cam["cam"], feats[k, 0], feats[k, 1]))
+        else:
+            assert not init[k, 1:4].any()
