@@ -69,6 +69,10 @@ def parse_args():
     ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather", "p2p"],
                     help="N > 1: NCCL all-gather of the r / J blocks to every rank, NCCL gather to rank 0, or p2p: pushes into "
                          "every peer's symmetric buffer by copy engines over NVLink")
+    ap.add_argument("--e2e-record", default="slim", choices=["slim", "full"],
+                    help="fields the end-to-end leg copies back: slim = idx, accepted, type, abcd + r, J (70 B/query: the caller holds the "
+                         "cloud, xyz and dist follow from idx); full = the whole LidarPoint record as in round 1 (+ xyz, dist: 102 B/query)")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not bind the process to the CPUs next to its GPU")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (query-count sweeps only; the default line carries it)")
     ap.add_argument("--zbuf-scale", type=float, default=1.0, help="depth_image_scale of the depth-projection leg (reference default 0.2)")
     ap.add_argument("--zbuf-images", type=int, default=6, help="images per GPU of the depth-projection leg (0 = skip)")
@@ -404,6 +408,13 @@ def run_b200(args):
     n_cloud, Q, desc = workload_sizes(args)
     ctx = pcd.Context(local)
     dev = torch.device("cuda", local)
+    # Pinned staging buffers and the threads that issue the copies stay on the GPU's NUMA node: bind this rank's
+    # process to the CPUs next to its GPU before anything is allocated (eight unbound ranks collapsed).
+    all_cpus = sorted(os.sched_getaffinity(0))
+    numa = {"bound": False, "cpus": len(all_cpus)}
+    if not args.no_numa_bind:
+        k = pcd.host_bind_near(local)
+        numa = {"bound": k > 0, "cpus": abs(k), "of": len(all_cpus)}
 
     # ---- cloud: generated on rank 0, replicated over NCCL/NVLink, indexed on every GPU -------------
     t_gen = time.perf_counter()
@@ -567,10 +578,12 @@ def run_b200(args):
     e2e_steps, e2e_s, h2d, d2h = 0, 1.0, 0, 0
     if not args.no_e2e:
         # ---- end to end: the host-pointer C ABI, pinned host buffers, H2D + D2H inside the timed region ----
-        fields = ("idx", "accepted", "type", "xyz", "abcd", "dist")
+        fields = ("idx", "accepted", "type", "abcd") if args.e2e_record == "slim" else ("idx", "accepted", "type", "xyz", "abcd", "dist")
         shapes = {"idx": ((Q,), np.int32), "accepted": ((Q,), np.uint8), "type": ((Q,), np.uint8), "xyz": ((Q, 3), np.float64),
                   "abcd": ((Q, 4), np.float64), "dist": ((Q,), np.float64)}
         h_out = {f: pcd.pinned_empty(*shapes[f]) for f in fields}
+        for v in h_out.values():
+            v[...] = 0                                   # first touch on this rank's NUMA node
         h_w = pcd.pinned_empty((Q,), np.float64)
         h_r = pcd.pinned_empty((Q,), np.float64)
         h_J = pcd.pinned_empty((Q, 3), np.float64)
@@ -613,7 +626,10 @@ def run_b200(args):
                      "clocks": clocks,
                      "e2e": None if args.no_e2e else {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
                              "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                             "record": f"{args.e2e_record}: " + ", ".join(fields) + " + r, J",
+                             "per_rank_gbps": {"h2d": h2d * e2e_steps / e2e_s / 1e9, "d2h": d2h * e2e_steps / e2e_s / 1e9},
                              "api": "pcd_associate_evaluate_batch (host pointers, pinned; chunked H2D / kernels / D2H pipeline)"},
+                     "numa": numa,
                      "roofline": {"bound": "hbm", "kernel": "k_nn_search + k_nn_far (two CUDA-event spans per pass, added)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                   "frac": achieved / peak,
                                   "traffic": NCU_TRAFFIC_NN_SWEEP50M if (args.workload == "sweep50m" and Q == 16_000_000 and n_cloud == 50_000_000) else None,
@@ -631,6 +647,7 @@ def run_b200(args):
         if zb is not None:
             line["zbuffer"] = zb
         if world == 1 and not args.no_cpu_baseline:
+            os.sched_setaffinity(0, all_cpus)             # the CPU baseline uses every core the process is allowed
             orc = load_oracle()
             cb, _ = cpu_baseline(orc, world_cloud, q_np, on_np, args.cpu_seconds)
             line["cpu_baseline"] = cb

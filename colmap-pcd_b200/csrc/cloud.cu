@@ -1,5 +1,6 @@
 // cloud.cu -- cloud upload (a1/a2), NN grid index build (a3) and 1 m sub-map build (a9).
 #include "common.cuh"
+#include <string>
 #include <cub/cub.cuh>
 #include <math.h>
 #include <stdlib.h>
@@ -145,7 +146,9 @@ __global__ void k_sub_decode(const unsigned long long* __restrict__ ukeys, int64
 int upload_common(pcd_ctx* ctx, const float* d_in, int64_t n, int direction_trans, pcd_cloud** out) {
   // d_in: device AoS8 (raw).  Produces the compacted post-swap cloud.
   cudaStream_t st = ctx->stream;
-  pcd_cloud* c = new pcd_cloud();
+  // released again on every early return below (PCD_CUDA returns on a CUDA error)
+  struct Guard { pcd_cloud* c; ~Guard() { if (c) { cudaFree(c->aos); delete c; } } } guard{new pcd_cloud()};
+  pcd_cloud* c = guard.c;
   c->ctx = ctx;
   int64_t m = n;
   if (n > 0) {
@@ -173,6 +176,7 @@ int upload_common(pcd_ctx* ctx, const float* d_in, int64_t n, int direction_tran
   }
   c->n = m;
   *out = c;
+  guard.c = nullptr;
   return PCD_OK;
 }
 
@@ -443,7 +447,7 @@ int pcd_submap_build(pcd_cloud* c, const pcd_proj_options* opt) {
     if (b - a >= 2097151.0 || fabs(a) > 1e9 || fabs(b) > 1e9) PCD_FAIL(ctx, PCD_E_INVALID, "sub-map key range too large on axis %d", d);
     k0[d] = (int)a;
   }
-  pcd::DevBuf k64a, k64b;   // local: 8 B keys
+  struct Scratch : pcd::DevBuf { ~Scratch() { release(); } } k64a, k64b;   // local 8 B keys, freed on every return path
   PCD_CUDA(ctx, k64a.ensure(8 * (size_t)n)); PCD_CUDA(ctx, k64b.ensure(8 * (size_t)n));
   PCD_CUDA(ctx, ctx->vals.ensure(4 * (size_t)n)); PCD_CUDA(ctx, ctx->vals_alt.ensure(4 * (size_t)n));
   cub::DoubleBuffer<unsigned long long> kb(k64a.as<unsigned long long>(), k64b.as<unsigned long long>());
@@ -514,6 +518,41 @@ int pcd_cloud_load_ply(pcd_ctx* ctx, const char* path, const pcd_proj_options* o
   rc = pcd_cloud_from_host(ctx, host, n, 1, out);
   pcd_free(host);
   if (rc) return rc;
+  rc = pcd_index_build(*out, 0.0f);
+  if (!rc && opt) rc = pcd_submap_build(*out, opt);
+  if (rc) { pcd_cloud_destroy(*out); *out = nullptr; }
+  return rc;
+}
+
+// N3 (src/controllers/bundle_adjustment.cc:123-124 re-loads and re-indexes the map on every refine): the parsed,
+// axis-swapped, NaN-compacted cloud is kept in a binary sidecar next to the PLY (path + ".pcdb200", keyed by the source
+// file's size, mtime and head / tail bytes).  A hit skips the PLY parse and PointCloudDirectionTrans; the two GPU
+// indices are always rebuilt (tens of milliseconds, far less than reading a table of their size back).
+int pcd_cloud_load_ply_cached(pcd_ctx* ctx, const char* path, const pcd_proj_options* opt, pcd_cloud** out, int* cache_hit) {
+  if (!ctx || !path || !out) PCD_FAIL(ctx, PCD_E_INVALID, "pcd_cloud_load_ply_cached: bad argument");
+  if (cache_hit) *cache_hit = 0;
+  *out = nullptr;
+  uint64_t key = 0;
+  int rc = pcd_file_key(path, &key);
+  if (rc) { ctx->err = pcd_last_error(nullptr); return rc; }
+  const std::string side = std::string(path) + ".pcdb200";
+  float* host = nullptr; int64_t n = 0;
+  if (pcd_sidecar_read(side.c_str(), key, 1, &host, &n) == PCD_OK) {
+    rc = pcd_cloud_from_host(ctx, host, n, 0, out);            // already in the index space: no swap, no compaction
+    pcd_free(host);
+    if (rc) return rc;
+    if (cache_hit) *cache_hit = 1;
+  } else {
+    rc = pcd_ply_read(path, &host, &n);
+    if (rc) { ctx->err = pcd_last_error(nullptr); return rc; }
+    rc = pcd_cloud_from_host(ctx, host, n, 1, out);
+    pcd_free(host);
+    if (rc) return rc;
+    const int64_t m = (*out)->n;                              // best effort: a read-only directory just means no sidecar
+    float* swapped = (float*)malloc(m > 0 ? 32 * (size_t)m : 32);
+    if (swapped && pcd_cloud_download(*out, swapped) == PCD_OK) pcd_sidecar_write(side.c_str(), key, 1, swapped, m);
+    free(swapped);
+  }
   rc = pcd_index_build(*out, 0.0f);
   if (!rc && opt) rc = pcd_submap_build(*out, opt);
   if (rc) { pcd_cloud_destroy(*out); *out = nullptr; }

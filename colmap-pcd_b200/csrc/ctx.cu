@@ -9,6 +9,8 @@ void set_global_error(const std::string& s) { g_err = s; }
 
 extern "C" {
 
+void pcd_ctx_destroy(pcd_ctx* c);
+
 int pcd_ctx_create(int device, pcd_ctx** out) {
   if (!out) PCD_FAIL((pcd_ctx*)nullptr, PCD_E_INVALID, "pcd_ctx_create: out is NULL");
   *out = nullptr;
@@ -28,10 +30,14 @@ int pcd_ctx_create(int device, pcd_ctx** out) {
   pcd_ctx* c = new pcd_ctx();
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
-  PCD_CUDA((pcd_ctx*)nullptr, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  PCD_CUDA((pcd_ctx*)nullptr, cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking));
-  PCD_CUDA((pcd_ctx*)nullptr, cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking));
-  for (int i = 0; i < 8; i++) PCD_CUDA((pcd_ctx*)nullptr, cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming));
+  cudaError_t ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->copy_in, cudaStreamNonBlocking);
+  if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->copy_out, cudaStreamNonBlocking);
+  for (int i = 0; i < 8 && ce == cudaSuccess; i++) ce = cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming);
+  if (ce != cudaSuccess) {
+    pcd_ctx_destroy(c);                                      // whatever was created so far
+    PCD_FAIL((pcd_ctx*)nullptr, PCD_E_CUDA, "creating the context's streams / events failed: %s", cudaGetErrorString(ce));
+  }
   *out = c;
   return PCD_OK;
 }

@@ -310,6 +310,33 @@ int main(int argc, char** argv) {
       return true;
     };
     if (cache.size() != 2 || !same(cache[7], m) || !same(cache[9], m2)) { fprintf(stderr, "batched SetNewImages differs from SetNewImage\n"); return 1; }
+    // (5) Project2Image over a mock reconstruction: image 9 (the shifted pose) is reached through a pair above the
+    // threshold, image 11 through a pair at the threshold (skipped), image 7 is cached already
+    {
+      struct El { uint32_t image_id; };
+      struct TrackT { std::vector<El> e; const std::vector<El>& Elements() const { return e; } };
+      struct P3 { TrackT t; const TrackT& Track() const { return t; } };
+      struct Pair { size_t num_total_corrs; };
+      struct Recon {
+        std::map<uint64_t, P3> pts; MockCamera cam; std::map<uint32_t, size_t> pairs;
+        P3& Point3D(uint64_t id) { return pts[id]; }
+        bool ExistsImagePair(uint32_t, uint32_t b) { return pairs.count(b) != 0; }
+        Pair ImagePair(uint32_t, uint32_t b) { return Pair{pairs[b]}; }
+        struct Img : MockImage { uint32_t CameraId() const { return 0; } };
+        std::map<uint32_t, Img> ims;
+        Img& Image(uint32_t id) { return ims[id]; }
+        MockCamera& Camera(uint32_t) { return cam; }
+      } rec;
+      rec.cam = cam;
+      static_cast<MockImage&>(rec.ims[7]) = image; static_cast<MockImage&>(rec.ims[9]) = image2; static_cast<MockImage&>(rec.ims[11]) = image2;
+      rec.pairs[9] = 31; rec.pairs[11] = 30;
+      rec.pts[1].t.e = {{7}, {9}, {11}}; rec.pts[2].t.e = {{9}, {7}};
+      std::map<uint64_t, std::map<uint64_t, Eigen::Vector6d>> cache2;
+      cache2[7] = m;
+      std::vector<uint64_t> pids = {1, 2};
+      const size_t np = Project2Image(pcp, &rec, pids, 7u, 30, cache2);
+      if (np != 1 || cache2.size() != 2 || !same(cache2[9], m2)) { fprintf(stderr, "Project2Image selected %zu images\n", np); return 1; }
+    }
     // (4) the initial-pair overload (src/lidar/pcd_projection.cc:102-220): one push_back per keypoint after what the vector held
     std::vector<std::pair<Eigen::Vector2d, bool>> pt_xys;
     for (int64_t i = 0; i < nf; i++) pt_xys.push_back({Eigen::Vector2d{im[18 + 2 * i], im[19 + 2 * i]}, false});

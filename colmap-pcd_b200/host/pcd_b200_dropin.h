@@ -19,12 +19,14 @@
 // There is no CPU fallback anywhere in this file: every numeric result comes from libpcd_b200.so.
 #pragma once
 #include <stdint.h>
+#include <stdlib.h>
 #include <array>
 #include <cmath>
 #include <map>
 #include <memory>
 #include <mutex>
 #include <string>
+#include <type_traits>
 #include <utility>
 #include <vector>
 #include "../../include/pcd_b200.h"
@@ -114,31 +116,52 @@ typedef std::shared_ptr<LidarPointcloud> LidarPointcloudPtr;
 // One CUDA context per process and device, shared by every shim object (the reference's objects are
 // all owned by one controller thread; batch calls on a context are serialised by `mu`).
 struct DropinRuntime {
-  pcd_ctx* ctx = nullptr;
+  pcd_ctx* ctx = nullptr;            // the first device's context (all serial calls)
+  pcd_group* group = nullptr;        // more than one device: the batched calls are sharded over the group
+  std::vector<int> devices;          // SetDevices(), or the environment variable PCD_B200_DEVICES="0,1,2,3"; default: device 0
   std::mutex mu;
   std::string error;
   static DropinRuntime& Get() { static DropinRuntime r; return r; }
+  void SetDevices(const std::vector<int>& d) { std::lock_guard<std::mutex> g(mu); if (!ctx) devices = d; }
   bool Ensure() {
     std::lock_guard<std::mutex> g(mu);
     if (ctx) return true;
-    if (pcd_ctx_create(0, &ctx) != PCD_OK) { error = pcd_last_error(nullptr); ctx = nullptr; return false; }
+    if (devices.empty()) {
+      if (const char* e = getenv("PCD_B200_DEVICES")) { for (const char* p = e; *p;) { devices.push_back(atoi(p)); while (*p && *p != ',') p++; if (*p) p++; } }
+      if (devices.empty()) devices.push_back(0);
+    }
+    if (devices.size() > 1) {
+      if (pcd_group_create(devices.data(), (int)devices.size(), &group) != PCD_OK) { error = pcd_last_error(nullptr); group = nullptr; return false; }
+      ctx = pcd_group_ctx(group, 0);
+      return true;
+    }
+    if (pcd_ctx_create(devices[0], &ctx) != PCD_OK) { error = pcd_last_error(nullptr); ctx = nullptr; return false; }
     return true;
   }
-  ~DropinRuntime() { if (ctx) pcd_ctx_destroy(ctx); }
+  ~DropinRuntime() { if (group) pcd_group_destroy(group); else if (ctx) pcd_ctx_destroy(ctx); }
   // A context of the calling thread's own (streams and scratch are per context), for the small per-record calls a
   // serial call site or a Ceres worker thread makes: no process-wide lock is taken on that path.
   static pcd_ctx* Thread() {
     struct Holder { pcd_ctx* c = nullptr; ~Holder() { if (c) pcd_ctx_destroy(c); } };
     static thread_local Holder h;
-    if (!h.c && pcd_ctx_create(0, &h.c) != PCD_OK) h.c = nullptr;
+    if (!h.c && pcd_ctx_create(Get().devices.empty() ? 0 : Get().devices[0], &h.c) != PCD_OK) h.c = nullptr;
     return h.c;
   }
 };
 
 // Device-resident cloud shared between Kdtree and PcdProj (the reference keeps three host copies).
 struct DeviceCloud {
-  pcd_cloud* h = nullptr;
-  ~DeviceCloud() { if (h) pcd_cloud_destroy(h); }
+  pcd_cloud* h = nullptr;            // on the first device
+  pcd_group_cloud* gc = nullptr;     // replicas on every device of the group (owns h once it exists)
+  // after the index and the sub-map are built: copy them to the other devices of the group
+  bool Replicate() {
+    DropinRuntime& rt = DropinRuntime::Get();
+    if (!rt.group || gc || !h) return true;
+    std::lock_guard<std::mutex> g(rt.mu);
+    if (pcd_group_replicate(rt.group, h, &gc) != PCD_OK) { rt.error = pcd_group_last_error(rt.group); gc = nullptr; return false; }
+    return true;
+  }
+  ~DeviceCloud() { if (gc) pcd_group_cloud_destroy(gc); else if (h) pcd_cloud_destroy(h); }
 };
 
 struct PcdProjectionOptions {        // src/lidar/pcd_projection.h:31-47, same fields and defaults
@@ -211,6 +234,7 @@ class Kdtree {                       // src/lidar/kdtree.h:13-22
   }
   void SetHostCloud(const LidarPointcloudPtr& p) { global_pointcloud_ptr_ = p; }
   pcd_cloud* handle() const { return dev_ ? dev_->h : nullptr; }
+  pcd_group_cloud* group_handle() const { return dev_ ? dev_->gc : nullptr; }
  private:
   LidarPointcloudPtr global_pointcloud_ptr_;
   std::shared_ptr<DeviceCloud> dev_;
@@ -281,9 +305,9 @@ class PcdProj {                      // src/lidar/pcd_projection.h:49-66
       std::lock_guard<std::mutex> g(rt.mu);
       pcd_proj_options o = options_.ToC();
       double* coef = SplatCoef(ims[0], o);
-      if (pcd_project_images(dev_->h, ims.data(), (int64_t)ims.size(), coef, feat.data(), start.data(), win.data(), rng.data(), nullptr) != PCD_OK) {
-        rt.error = pcd_last_error(rt.ctx); return;
-      }
+      const int rc = dev_->gc ? pcd_group_project_images(dev_->gc, ims.data(), (int64_t)ims.size(), coef, feat.data(), start.data(), win.data(), rng.data(), nullptr)
+                              : pcd_project_images(dev_->h, ims.data(), (int64_t)ims.size(), coef, feat.data(), start.data(), win.data(), rng.data(), nullptr);
+      if (rc != PCD_OK) { rt.error = pcd_last_error(rt.ctx); return; }
     }
     for (size_t k = 0; k < images.size(); k++) {
       auto& map = cache[(typename CacheT::key_type)image_ids[k]];
@@ -395,6 +419,7 @@ class PointCloudProcess {            // src/lidar/ply.h:13-40
     kdtree_ptr_ = std::make_shared<Kdtree>();
     kdtree_ptr_->SetHostCloud(global_pcd_ptr_);
     kdtree_ptr_->Attach(dc);
+    if (!dc->Replicate()) return false;                       // several devices: index and sub-map copied, not rebuilt
     return pcd_proj_->handle() != nullptr && kdtree_ptr_->handle() != nullptr;
   }
   // ply.cc:90-107
@@ -490,6 +515,42 @@ class LidarPoint {
 };
 #endif
 
+// BundleAdjustmentConfig::Project2Image (src/optim/bundle_adjustment.cc:241-281) for a whole set of variable points:
+// the reference's decision, element by element (pcd_project2image_select: skip an image whose pair with the new image
+// has <= match_features_threshold correspondences, :247-253; skip what lidar_searched_image_ids_ already holds), then
+// ONE batched projection of everything selected instead of one SetNewImage per image.  ReconstructionT is
+// colmap::Reconstruction (Point3D(id).Track().Elements(), ExistsImagePair, ImagePair().num_total_corrs, Image(), Camera()).
+template <typename ReconstructionT, typename PointIds, typename CacheT>
+inline size_t Project2Image(lidar::PointCloudProcess& pcp, ReconstructionT* reconstruction, const PointIds& point3D_ids,
+                            uint32_t image_id, int match_features_threshold, CacheT& lidar_searched_image_ids_) {
+  std::vector<uint32_t> todo;
+  for (const auto point3D_id : point3D_ids) {
+    const auto& track_els = reconstruction->Point3D(point3D_id).Track().Elements();
+    const int64_t n = (int64_t)track_els.size();
+    std::vector<uint32_t> img((size_t)n); std::vector<int64_t> corrs((size_t)n); std::vector<uint8_t> cached((size_t)n), sel((size_t)n);
+    for (int64_t k = 0; k < n; k++) {
+      const uint32_t id2 = (uint32_t)track_els[(size_t)k].image_id;
+      img[(size_t)k] = id2;
+      corrs[(size_t)k] = (id2 != image_id && reconstruction->ExistsImagePair(image_id, id2)) ? (int64_t)reconstruction->ImagePair(image_id, id2).num_total_corrs : -1;
+      bool have = lidar_searched_image_ids_.find(id2) != lidar_searched_image_ids_.end();
+      for (uint32_t t : todo) have = have || t == id2;
+      cached[(size_t)k] = have ? 1 : 0;
+    }
+    if (pcd_project2image_select(img.data(), n, image_id, corrs.data(), match_features_threshold, cached.data(), sel.data()) < 0) return 0;
+    for (int64_t k = 0; k < n; k++) if (sel[(size_t)k]) todo.push_back(img[(size_t)k]);
+  }
+  if (todo.empty() || !pcp.pcd_proj_) return 0;
+  typedef typename std::remove_reference<decltype(reconstruction->Image(todo[0]))>::type ImageT;
+  typedef typename std::remove_reference<decltype(reconstruction->Camera(reconstruction->Image(todo[0]).CameraId()))>::type CameraT;
+  std::vector<const ImageT*> images; std::vector<const CameraT*> cameras; std::vector<uint64_t> ids;
+  for (uint32_t id : todo) {
+    const ImageT& image = reconstruction->Image(id);
+    images.push_back(&image); cameras.push_back(&reconstruction->Camera(image.CameraId())); ids.push_back(id);
+  }
+  pcp.pcd_proj_->template SetNewImages<ImageT, CameraT>(images, cameras, ids, lidar_searched_image_ids_);
+  return todo.size();
+}
+
 // Batched replacement of the three serial association loops (src/sfm/incremental_mapper.cc:1138-1166,
 // :1411-1470; src/controllers/bundle_adjustment.cc:126-185).  ids / xyz: the variable points in the
 // caller's iteration order; returns the accepted matches keyed by point id.
@@ -506,10 +567,12 @@ inline bool MatchClosestLidarPoints(lidar::PointCloudProcess& pcp, const std::ve
   {
     std::lock_guard<std::mutex> g(rt.mu);
     const bool sweep = variant != PCD_ASSOC_WHOLE_MAP;
-    if (pcd_associate_batch(pcp.kdtree_ptr_->handle(), xyz.data(), nullptr, sweep ? global_opt_num.data() : nullptr,
-                            sweep ? &sw : nullptr, n, variant, &o) != PCD_OK) {
-      rt.error = pcd_last_error(rt.ctx); return false;
-    }
+    pcd_group_cloud* gc = pcp.kdtree_ptr_->group_handle();
+    const int rc = gc ? pcd_group_associate_evaluate_batch(gc, xyz.data(), nullptr, sweep ? global_opt_num.data() : nullptr, sweep ? &sw : nullptr,
+                                                           n, variant, 0.0, 0.0, 0.0, &o, nullptr, nullptr, nullptr)
+                      : pcd_associate_batch(pcp.kdtree_ptr_->handle(), xyz.data(), nullptr, sweep ? global_opt_num.data() : nullptr,
+                                            sweep ? &sw : nullptr, n, variant, &o);
+    if (rc != PCD_OK) { rt.error = gc ? pcd_group_last_error(rt.group) : pcd_last_error(rt.ctx); return false; }
   }
   for (int64_t i = 0; i < n; i++)
     if (acc[i]) out->insert({ids[i], LidarPoint::FromBatch(o, i)});

@@ -216,6 +216,16 @@ class Cloud:
                   "pcd_cloud_load_ply")
         return self
 
+    @classmethod
+    def load_ply_cached(cls, ctx, path, opt=None):
+        """pcd_cloud_load_ply_cached: (cloud, cache_hit)."""
+        h = C.c_void_p(); hit = C.c_int()
+        ctx.check(lib().pcd_cloud_load_ply_cached(ctx._h, path.encode(), C.byref(opt) if opt is not None else None, C.byref(h), C.byref(hit)),
+                  "pcd_cloud_load_ply_cached")
+        c = cls.__new__(cls)
+        c.ctx, c._h, c.opt = ctx, h, opt
+        return c, bool(hit.value)
+
     def close(self):
         if self._h:
             lib().pcd_cloud_destroy(self._h)
@@ -357,6 +367,46 @@ class Cloud:
         return m.astype(bool), xyz
 
 
+def project2image_select(track_image, image_id, pair_corrs, threshold, cached=None):
+    """pcd_project2image_select: flags of the track elements whose images must be projected now, and their count."""
+    t = np.ascontiguousarray(track_image, dtype=np.uint32); pc = np.ascontiguousarray(pair_corrs, dtype=np.int64)
+    c = None if cached is None else np.ascontiguousarray(cached, dtype=np.uint8)
+    sel = np.zeros(len(t), dtype=np.uint8)
+    lib().pcd_project2image_select.restype = C.c_int64
+    n = lib().pcd_project2image_select(_ptr(t), C.c_int64(len(t)), C.c_uint32(image_id), _ptr(pc), C.c_int(threshold), _ptr(c), _ptr(sel))
+    if n < 0:
+        raise PcdError("pcd_project2image_select: bad argument")
+    return sel, int(n)
+
+
+def file_key(path):
+    k = C.c_uint64()
+    if lib().pcd_file_key(path.encode(), C.byref(k)):
+        raise PcdError(lib().pcd_last_error(None).decode())
+    return k.value
+
+
+def sidecar_write(path, key, aos8, direction_trans=True):
+    a = np.ascontiguousarray(aos8, dtype=np.float32).reshape(-1, 8)
+    if lib().pcd_sidecar_write(path.encode(), C.c_uint64(key), C.c_int(int(direction_trans)), _ptr(a), C.c_int64(len(a))):
+        raise PcdError(lib().pcd_last_error(None).decode())
+
+
+def sidecar_read(path, key, direction_trans=True):
+    """The cloud of a sidecar, or None when it is missing / damaged / belongs to another source file."""
+    p = C.POINTER(C.c_float)(); n = C.c_int64()
+    if lib().pcd_sidecar_read(path.encode(), C.c_uint64(key), C.c_int(int(direction_trans)), C.byref(p), C.byref(n)):
+        return None
+    out = np.ctypeslib.as_array(p, shape=(n.value * 8,)).copy().reshape(-1, 8) if n.value else np.zeros((0, 8), np.float32)
+    lib().pcd_free(p)
+    return out
+
+
+def host_bind_near(device):
+    """Binds the calling thread (and what it allocates next) to the CPUs next to `device`; > 0: CPUs bound to, < 0: unchanged."""
+    return int(lib().pcd_host_bind_near(C.c_int(device)))
+
+
 def pinned_empty(shape, dtype):
     """numpy array over cudaMallocHost memory (pcd_host_alloc); freed when the array is collected."""
     dtype = np.dtype(dtype)
@@ -415,3 +465,63 @@ def pose_ply_write(path, xyzrpy):
     rc = lib().pcd_pose_ply_write(path.encode(), _ptr(a), C.c_int64(len(a)))
     if rc:
         raise PcdError(lib().pcd_last_error(None).decode())
+
+
+class Group:
+    """pcd_group_*: the path sharded over several devices of one node behind the C ABI (a device may repeat)."""
+
+    def __init__(self, devices):
+        self.devices = list(devices)
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        self._h = C.c_void_p()
+        rc = lib().pcd_group_create(arr, C.c_int(len(self.devices)), C.byref(self._h))
+        if rc:
+            raise PcdError(f"pcd_group_create: {lib().pcd_last_error(None).decode()}")
+        lib().pcd_group_last_error.restype = C.c_char_p
+        lib().pcd_group_last_error.argtypes = [C.c_void_p]
+        lib().pcd_group_destroy.restype = None
+        lib().pcd_group_cloud_destroy.restype = None
+        self._gc = None
+        self.opt = None
+
+    def _check(self, rc, what):
+        if rc:
+            raise PcdError(f"{what}: {lib().pcd_group_last_error(self._h).decode()}")
+
+    def cloud_from_host(self, aos8, direction_trans=False, cell_size=0.0, opt=None):
+        a = np.ascontiguousarray(aos8, dtype=np.float32).reshape(-1, 8)
+        gc = C.c_void_p()
+        self._check(lib().pcd_group_cloud_from_host(self._h, _ptr(a), C.c_int64(len(a)), C.c_int(int(direction_trans)), C.c_float(cell_size),
+                                                    C.byref(opt) if opt is not None else None, C.byref(gc)), "pcd_group_cloud_from_host")
+        self._gc, self.opt = gc, opt
+
+    def associate_evaluate(self, p, weights, range_=None, opt_num=None, sweep=None, variant=ASSOC_LOCAL):
+        p = _f64(p, 3); n = len(p)
+        rng = None if range_ is None else _f64(range_).ravel()
+        on = None if opt_num is None else np.ascontiguousarray(opt_num, dtype=np.int32)
+        sw = None if sweep is None else RangeSweep(*sweep)
+        o = {"idx": np.empty(n, np.int32), "accepted": np.empty(n, np.uint8), "type": np.empty(n, np.uint8), "rgb": np.empty((n, 3), np.uint8),
+             "xyz": np.empty((n, 3)), "abcd": np.empty((n, 4)), "dist": np.empty(n), "angle": np.empty(n)}
+        out = AssocOut(*[_ptr(o[k]) for k in ("idx", "accepted", "type", "rgb", "xyz", "abcd", "dist", "angle")])
+        r = np.empty(n); J = np.empty((n, 3)); s = C.c_double()
+        self._check(lib().pcd_group_associate_evaluate_batch(self._gc, _ptr(p), _ptr(rng), _ptr(on), C.byref(sw) if sw is not None else None,
+                                                             C.c_int64(n), C.c_int(variant), C.c_double(weights[0]), C.c_double(weights[1]),
+                                                             C.c_double(weights[2]), C.byref(out), _ptr(r), _ptr(J), C.byref(s)),
+                    "pcd_group_associate_evaluate_batch")
+        return o, r, J, s.value
+
+    def project_images(self, images, coef, feat_xy, feat_start):
+        arr = (Image * len(images))(*images)
+        coef_c = (C.c_double * 4)(*coef)
+        f = _f64(feat_xy, 2); fs = np.ascontiguousarray(feat_start, dtype=np.int64)
+        nf = len(f)
+        widx = np.empty(nf, dtype=np.int32); wr = np.empty(nf, dtype=np.float32); stats = np.zeros(4, dtype=np.int64)
+        self._check(lib().pcd_group_project_images(self._gc, arr, C.c_int64(len(images)), coef_c, _ptr(f), _ptr(fs), _ptr(widx), _ptr(wr),
+                                                   _ptr(stats)), "pcd_group_project_images")
+        return widx, wr, stats
+
+    def close(self):
+        if self._gc is not None:
+            lib().pcd_group_cloud_destroy(self._gc); self._gc = None
+        if self._h:
+            lib().pcd_group_destroy(self._h); self._h = None

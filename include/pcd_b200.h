@@ -114,6 +114,23 @@ PCD_API int pcd_cloud_from_host(pcd_ctx* ctx, const float* aos8, int64_t n, int 
 PCD_API int pcd_cloud_from_device(pcd_ctx* ctx, const float* d_aos8, int64_t n, int direction_trans, pcd_cloud** out);
 /* pcd_ply_read + pcd_cloud_from_host(direction_trans = 1) + pcd_index_build + pcd_submap_build. */
 PCD_API int pcd_cloud_load_ply(pcd_ctx* ctx, const char* path, const pcd_proj_options* opt, pcd_cloud** out);
+/* N3, one-time load (the reference re-parses and re-indexes the map on every refine,
+ * src/controllers/bundle_adjustment.cc:123-124): as pcd_cloud_load_ply, but the parsed, axis-swapped, NaN-compacted cloud
+ * is kept in a binary sidecar path + ".pcdb200" keyed by the source file (pcd_file_key); *cache_hit = 1 when it was used.
+ * A stale, truncated or foreign sidecar is ignored and rewritten.  The GPU indices are rebuilt either way. */
+PCD_API int pcd_cloud_load_ply_cached(pcd_ctx* ctx, const char* path, const pcd_proj_options* opt, pcd_cloud** out, int* cache_hit);
+PCD_API int pcd_file_key(const char* path, uint64_t* key);      /* FNV-1a of size, mtime, first and last 64 KiB */
+PCD_API int pcd_sidecar_write(const char* path, uint64_t key, int direction_trans, const float* aos8, int64_t n);
+PCD_API int pcd_sidecar_read(const char* path, uint64_t key, int direction_trans, float** aos8, int64_t* n);   /* pcd_free() */
+
+/* a16, the decision half of BundleAdjustmentConfig::Project2Image (src/optim/bundle_adjustment.cc:241-281): for one
+ * point's track, which elements' images go to SetNewImage now.  track_image[k]: the element's image; pair_corrs[k]:
+ * num_total_corrs of the pair (image_id, track_image[k]), -1 when the pair does not exist; cached[k] != 0 (or cached ==
+ * NULL: none): already in lidar_searched_image_ids_.  An element is skipped iff its image differs from image_id, the pair
+ * exists and corrs <= match_features_threshold (:247-253); otherwise it is projected unless cached or already selected
+ * by an earlier element of the same track.  Returns the number selected (>= 0) or a negative status. */
+PCD_API int64_t pcd_project2image_select(const uint32_t* track_image, int64_t n, uint32_t image_id, const int64_t* pair_corrs,
+                                         int match_features_threshold, const uint8_t* cached, uint8_t* project);
 PCD_API void pcd_cloud_destroy(pcd_cloud* cloud);
 PCD_API int64_t pcd_cloud_size(const pcd_cloud* cloud);
 PCD_API int pcd_cloud_download(const pcd_cloud* cloud, float* aos8);   /* the post-swap cloud */
@@ -261,6 +278,42 @@ PCD_API int pcd_project_images(pcd_cloud* cloud, const pcd_image* imgs, int64_t 
 /* SetNewImage init overload's ray/plane step (src/lidar/pcd_projection.cc:183-205). */
 PCD_API int pcd_ray_plane_batch(pcd_cloud* cloud, const pcd_image* img, const double* feat_xy, const int32_t* winner_idx,
                                 int64_t n_feat, uint8_t* matched, double* xyz);
+
+/* ---------------------------------------------------------------- several GPUs of one node */
+/* A group is one context per device.  The cloud and both indices are built once on the group's first device and
+ * replicated device-to-device (peer copies over NVLink); a batch is cut into contiguous query shards (association) or
+ * image runs (projection), one per device, each an ordinary single-device call on a host thread bound to the CPUs next
+ * to its GPU.  Results land in the caller's host arrays at the shards' offsets: the consumer is one host process
+ * (Ceres, src/optim/bundle_adjustment.cc:452-530), so the gather of the residual / Jacobian blocks is the shards' own
+ * D2H copies over each GPU's PCIe link, and the one reduction (sum r^2, counters) is added on the host in rank order.
+ * devices == NULL: devices 0 .. n-1.  A device may be named more than once (several shards on one GPU). */
+typedef struct pcd_group pcd_group;
+typedef struct pcd_group_cloud pcd_group_cloud;
+PCD_API int pcd_group_create(const int* devices, int n, pcd_group** out);
+PCD_API void pcd_group_destroy(pcd_group* g);
+PCD_API int pcd_group_size(const pcd_group* g);
+PCD_API pcd_ctx* pcd_group_ctx(pcd_group* g, int rank);
+PCD_API const char* pcd_group_last_error(const pcd_group* g);
+/* cloud + NN index (+ sub-map when opt != NULL) on every device of the group */
+PCD_API int pcd_group_cloud_from_host(pcd_group* g, const float* aos8, int64_t n, int direction_trans, float cell_size,
+                                      const pcd_proj_options* opt, pcd_group_cloud** out);
+PCD_API int pcd_group_cloud_load_ply(pcd_group* g, const char* path, const pcd_proj_options* opt, pcd_group_cloud** out);
+/* replicates a cloud of the group's first context (ownership passes to the group cloud on success) */
+PCD_API int pcd_group_replicate(pcd_group* g, pcd_cloud* first, pcd_group_cloud** out);
+PCD_API pcd_cloud* pcd_group_cloud_rank(pcd_group_cloud* gc, int rank);
+PCD_API void pcd_group_cloud_destroy(pcd_group_cloud* gc);
+/* pcd_associate_evaluate_batch over the group (r == NULL: pcd_associate_batch); same arguments and results */
+PCD_API int pcd_group_associate_evaluate_batch(pcd_group_cloud* gc, const double* p_xyz, const double* range,
+                                               const int32_t* opt_num, const pcd_range_sweep* sweep, int64_t n, int variant,
+                                               double w_proj, double w_icp, double w_ground, const pcd_assoc_out* out,
+                                               double* r, double* J, double* sum_sq);
+/* pcd_project_images over the group (contiguous runs of images per device) */
+PCD_API int pcd_group_project_images(pcd_group_cloud* gc, const pcd_image* imgs, int64_t n_img, const double coef[4],
+                                     const double* feat_xy, const int64_t* feat_start, int32_t* winner_idx,
+                                     float* winner_range, int64_t* stats);
+/* Binds the calling thread to the CPUs next to `device` (sysfs local_cpulist): pinned buffers allocated afterwards and
+ * the copies issued from this thread stay on the GPU's NUMA node.  Returns the CPU count bound to (negative: unchanged). */
+PCD_API int pcd_host_bind_near(int device);
 
 #ifdef __cplusplus
 }

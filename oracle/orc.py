@@ -207,3 +207,13 @@ def ray_plane(cloud, gi, cam, u, v):
 
 def max_threads():
     return int(lib().orc_max_threads())
+
+
+def project2image(track_image, image_id, pair_corrs, threshold, cached_ids=()):
+    """Which track elements' images Project2Image hands to SetNewImage (src/optim/bundle_adjustment.cc:241-281)."""
+    t = np.ascontiguousarray(track_image, dtype=np.uint32); pc = np.ascontiguousarray(pair_corrs, dtype=np.int64)
+    c = np.ascontiguousarray(list(cached_ids), dtype=np.uint32); sel = np.zeros(len(t), dtype=np.uint8)
+    lib().orc_project2image.restype = C.c_int64
+    n = lib().orc_project2image(_p(t), C.c_int64(len(t)), C.c_uint32(image_id), _p(pc), C.c_int(threshold), _p(c) if len(c) else None,
+                                C.c_int64(len(c)), _p(sel))
+    return sel, int(n)

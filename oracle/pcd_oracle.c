@@ -729,3 +729,31 @@ ORC_API int orc_max_threads(void) {
   return 1;
 #endif
 }
+
+/* ------------------------------------------------------------------------------------------
+ * a16 BundleAdjustmentConfig::Project2Image, decision logic    src/optim/bundle_adjustment.cc:241-281
+ * Walks one point's track the way the reference does, with lidar_searched_image_ids_ modelled as a growing list:
+ * `cached` lists the image ids cached before the call (n_cached of them); selected[k] = 1 when element k's image is
+ * handed to SetNewImage (and thereby cached for the elements after it).  pair_corrs[k] < 0: no such image pair.
+ * ---------------------------------------------------------------------------------------- */
+ORC_API int64_t orc_project2image(const uint32_t* track_image, int64_t n, uint32_t image_id, const int64_t* pair_corrs,
+                                  int match_features_threshold, const uint32_t* cached, int64_t n_cached, uint8_t* selected) {
+  uint32_t* cache = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)(n_cached + n + 1));
+  int64_t nc = n_cached, count = 0;
+  for (int64_t i = 0; i < n_cached; i++) cache[i] = cached[i];
+  for (int64_t k = 0; k < n; k++) {
+    selected[k] = 0;
+    uint32_t image_id2 = track_image[k];
+    if (image_id2 != image_id) {
+      if (pair_corrs[k] >= 0) {                         /* reconstruction->ExistsImagePair(image_id, image_id2) */
+        size_t corrs = (size_t)pair_corrs[k];
+        if (corrs <= (size_t)match_features_threshold) continue;
+      }
+    }
+    int found = 0;                                       /* lidar_searched_image_ids_.find(track_el.image_id) */
+    for (int64_t i = 0; i < nc; i++) if (cache[i] == image_id2) { found = 1; break; }
+    if (!found) { selected[k] = 1; count++; cache[nc++] = image_id2; }
+  }
+  free(cache);
+  return count;
+}

@@ -344,3 +344,67 @@ def test_pose_ply_roundtrip_matches_reference_conversion(pcd, tmp_path):
         assert np.allclose(R_back, R_cw, atol=1e-12) and abs(np.linalg.norm(q) - 1) < 1e-12
     with pytest.raises(pcd.PcdError):
         pcd.pose_ply_read(str(tmp_path / "missing.ply"))
+
+
+def test_project2image_selection_logic(orc):
+    """a16: which images of a point's track BundleAdjustmentConfig::Project2Image projects
+    (src/optim/bundle_adjustment.cc:241-281) -- library (host logic, no GPU) vs the oracle's walk of the reference loop,
+    plus hand-worked cases."""
+    import __graft_entry__ as entry
+    pcd = entry.package()
+    # hand-worked: image 5 is the new image, threshold 30
+    #   el 0: image 5 itself            -> projected (not cached)
+    #   el 1: image 7, pair has 30      -> skipped (corrs <= threshold)
+    #   el 2: image 8, pair has 31      -> projected
+    #   el 3: image 9, no such pair     -> projected
+    #   el 4: image 8 again             -> already cached by el 2
+    #   el 5: image 6, pair has 500, cached before the call -> not projected
+    track = [5, 7, 8, 9, 8, 6]; corrs = [-1, 30, 31, -1, 31, 500]; cached = [0, 0, 0, 0, 0, 1]
+    sel, n = pcd.project2image_select(track, 5, corrs, 30, cached)
+    assert sel.tolist() == [1, 0, 1, 1, 0, 0] and n == 3
+    so, no = orc.project2image(track, 5, corrs, 30, cached_ids=[6])
+    assert so.tolist() == sel.tolist() and no == n
+    # a negative threshold converts to a huge size_t (the reference compares size_t <= int): every existing pair is skipped
+    sel, n = pcd.project2image_select([1, 2, 3], 1, [10, 10, -1], -1)
+    assert sel.tolist() == [1, 0, 1] and n == 2
+    rng = np.random.default_rng(4)
+    for _ in range(300):
+        m = int(rng.integers(0, 40))
+        track = rng.integers(0, 12, m).astype(np.uint32)
+        image_id = int(rng.integers(0, 12))
+        pair = {int(i): (int(rng.integers(0, 60)) if rng.random() < 0.7 else -1) for i in range(12)}
+        corrs = np.array([pair[int(t)] for t in track], np.int64)
+        cached_ids = [int(i) for i in range(12) if rng.random() < 0.3]
+        flags = np.array([int(t) in cached_ids for t in track], np.uint8)
+        thr = int(rng.integers(-1, 50))
+        sel, n = pcd.project2image_select(track, image_id, corrs, thr, flags)
+        so, no = orc.project2image(track, image_id, corrs, thr, cached_ids)
+        assert np.array_equal(sel, so) and n == no
+    assert pcd.project2image_select([], 0, [], 3)[1] == 0
+
+
+def test_sidecar_roundtrip_and_rejection(tmp_path, synth):
+    """N3: the sidecar of the parsed cloud -- exact round trip, and a stale / truncated / foreign file is refused."""
+    import __graft_entry__ as entry
+    pcd = entry.package()
+    raw, _ = synth.make_cloud(5000, seed=synth.SEED0 + 21)
+    src = str(tmp_path / "map.ply"); side = src + ".pcdb200"
+    pcd.ply_write(src, raw, binary=True)
+    key = pcd.file_key(src)
+    assert key == pcd.file_key(src)
+    assert pcd.sidecar_read(side, key) is None                       # missing
+    pcd.sidecar_write(side, key, raw)
+    got = pcd.sidecar_read(side, key)
+    assert got is not None and np.array_equal(got.view(np.uint32), raw.view(np.uint32))     # NaN normals and all
+    assert pcd.sidecar_read(side, key ^ 1) is None                    # another source file
+    assert pcd.sidecar_read(side, key, direction_trans=False) is None
+    data = open(side, "rb").read()
+    open(side, "wb").write(data[:-7])                                 # truncated
+    assert pcd.sidecar_read(side, key) is None
+    open(side, "wb").write(b"NOTASIDE" + data[8:])                    # foreign magic
+    assert pcd.sidecar_read(side, key) is None
+    raw2 = raw.copy(); raw2[0, 0] += 1.0
+    pcd.ply_write(src, raw2, binary=True)                             # the source changed: the key moves
+    assert pcd.file_key(src) != key
+    pcd.sidecar_write(side, key, np.zeros((0, 8), np.float32))
+    assert len(pcd.sidecar_read(side, key)) == 0

@@ -43,6 +43,14 @@ def test_dropin_shim_matches_oracle(tmp_path, orc, synth, pcd):
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     o = np.fromfile(str(tmp_path / "o.f64"))
+    # the same program over a two-rank group (PCD_B200_DEVICES; one GPU: two shards on device 0): identical dump
+    import torch
+    devs = "0,1" if torch.cuda.device_count() >= 2 else "0,0"
+    r2 = subprocess.run([EXE, ply, str(tmp_path / "q.f64"), str(tmp_path / "o2.f64"), str(tmp_path / "im.f64")],
+                        capture_output=True, text=True, env=dict(os.environ, PCD_B200_DEVICES=devs))
+    assert r2.returncode == 0, r2.stderr
+    o2 = np.fromfile(str(tmp_path / "o2.f64"))
+    assert np.array_equal(o, o2, equal_nan=True)
     pos = 0
     assert o[pos] == len(world); pos += 1
     tree = orc.KdTree(world)

@@ -503,3 +503,78 @@ def test_zbuffer_full_res_and_empty_frustum(scene, orc, synth, pcd, ctx):
     widx, _, z, stats = cl.project_image(far, coef, synth.make_features(100, cam=synth.OPENCV_1080), dense=True)
     assert stats[0] == 0 and (widx == -1).all() and (z == np.iinfo(np.uint64).max).all()
     cl.close()
+
+
+# ---------------------------------------------------------------- several devices behind the C ABI (pcd_group_*)
+def _group_devices():
+    import torch
+    n = torch.cuda.device_count()
+    return [0, 1] if n >= 2 else [0, 0]            # one GPU: two shards on the same device (two contexts)
+
+
+def test_group_association_equals_single_device(scene, orc, pcd, ctx):
+    """pcd_group_associate_evaluate_batch (cloud + index replicated by device-to-device copies, queries in contiguous
+    shards, one host thread per device) == pcd_associate_evaluate_batch on one device, bit for bit; sum r^2 is the
+    shards' sums added in rank order."""
+    rng_ = np.random.default_rng(9)
+    reps = 6
+    q = np.tile(scene["q"], (reps, 1)) + rng_.normal(0, 1e-3, (reps * len(scene["q"]), 3))
+    on = np.tile(scene["opt_num"], reps)
+    W = (10.0, 1000.0, 10000.0)
+    grp = pcd.Group(_group_devices())
+    try:
+        grp.cloud_from_host(scene["raw"], direction_trans=True)
+        o, r, J, s = grp.associate_evaluate(q, W, opt_num=on, sweep=(1.5, 0.2, 0.1), variant=pcd.ASSOC_GLOBAL)
+        rec, r1, J1, s1 = scene["cloud"].associate_evaluate(q, W, opt_num=on, sweep=(1.5, 0.2, 0.1), variant=pcd.ASSOC_GLOBAL)
+        for k in ("idx", "accepted", "type", "xyz", "abcd", "dist"):
+            assert np.array_equal(o[k], rec[k], equal_nan=(o[k].dtype.kind == "f")), k
+        assert np.array_equal(r, r1) and np.array_equal(J, J1, equal_nan=True)
+        half = len(q) // 2
+        _, _, _, sa = scene["cloud"].associate_evaluate(q[:half], W, opt_num=on[:half], sweep=(1.5, 0.2, 0.1), variant=pcd.ASSOC_GLOBAL)
+        _, _, _, sb = scene["cloud"].associate_evaluate(q[half:], W, opt_num=on[half:], sweep=(1.5, 0.2, 0.1), variant=pcd.ASSOC_GLOBAL)
+        assert s == sa + sb and _close(s, s1, 1e-12)
+        want = scene["tree"].associate(q, orc.search_range(on), variant=1)
+        assert np.array_equal(o["accepted"], want["accepted"])
+    finally:
+        grp.close()
+
+
+def test_group_projection_equals_single_device(scene, proj_scene, pcd, synth):
+    ps = proj_scene
+    feats = [synth.make_features(400 + 50 * k, seed=200 + k) for k in range(len(ps["cams"]))]
+    ims = [pcd.Image.make(c["qvec"], c["tvec"], c["cam"], c["width"], c["height"]) for c in ps["cams"]]
+    fs = np.concatenate([[0], np.cumsum([len(f) for f in feats])])
+    want = scene["cloud"].project_images(ims, ps["coef"], np.concatenate(feats), fs)
+    grp = pcd.Group(_group_devices())
+    try:
+        grp.cloud_from_host(scene["raw"], direction_trans=True, opt=pcd.ProjOptions.default())
+        got = grp.project_images(ims, ps["coef"], np.concatenate(feats), fs)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1].view(np.uint32), want[1].view(np.uint32))
+        assert np.array_equal(got[2], want[2])
+    finally:
+        grp.close()
+
+
+def test_cached_ply_load(tmp_path, scene, pcd, ctx, orc):
+    """N3: pcd_cloud_load_ply_cached -- first load parses the PLY and writes the sidecar, the second uses it; both give
+    the cloud, the index and the sub-map of the plain loader; a changed source file is parsed again."""
+    raw = scene["raw"][:60_000]
+    src = str(tmp_path / "map.ply")
+    pcd.ply_write(src, raw, binary=False)                              # ASCII: the expensive parse
+    opt = pcd.ProjOptions.default()
+    c0 = pcd.Cloud.load_ply(ctx, src, opt)
+    c1, hit1 = pcd.Cloud.load_ply_cached(ctx, src, opt)
+    c2, hit2 = pcd.Cloud.load_ply_cached(ctx, src, opt)
+    assert (hit1, hit2) == (False, True) and os.path.exists(src + ".pcdb200")
+    w0 = c0.download()
+    assert np.array_equal(c1.download().view(np.uint32), w0.view(np.uint32)) and np.array_equal(c2.download().view(np.uint32), w0.view(np.uint32))
+    q = scene["q"][:5000]
+    i0, d0 = c0.nn(q); i2, d2 = c2.nn(q)
+    assert np.array_equal(i0, i2) and np.array_equal(d0, d2)
+    bi, _ = orc.nn_brute(w0, q[:300])
+    assert np.array_equal(i2[:300], bi)
+    pcd.ply_write(src, raw[:50_000], binary=False)
+    c3, hit3 = pcd.Cloud.load_ply_cached(ctx, src, opt)
+    assert not hit3 and len(c3) < len(c0)
+    for c in (c0, c1, c2, c3):
+        c.close()
