@@ -142,6 +142,16 @@ struct pcd_cloud {
   uint32_t sub_seglen = pcd::SUBMAP_SEG;
 };
 
+// Debug build (make dbg -> libpcd_b200_dbg.so, -DPCD_DEBUG_CHECKS): device-side bounds assertions at every indexed
+// access of the search and projection kernels.  compute-sanitizer is closed on this pool, so this build plus
+// tools/sanitize_run.py is the memory check of the path (profiles/r02_debug_checks.log).  Compiled out otherwise.
+#ifdef PCD_DEBUG_CHECKS
+#include <assert.h>
+#define PCD_DASSERT(cond_) assert(cond_)
+#else
+#define PCD_DASSERT(cond_) ((void)0)
+#endif
+
 #define PCD_FAIL(ctx_, code_, ...)                                   \
   do {                                                               \
     char _b[512];                                                    \

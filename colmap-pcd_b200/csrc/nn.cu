@@ -102,6 +102,7 @@ struct Query {
   __device__ __forceinline__ void scan(const GridView& g, uint32_t b, uint32_t e, int first, int stride) {
     unsigned long long bst = best;
     for (uint32_t j = b + first; j < e; j += stride) {
+      PCD_DASSERT(j < g.n);
       float4 p = __ldg(&g.pts[j]);
       float ddx = qx - p.x, ddy = qy - p.y, ddz = qz - p.z;
       float d = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
@@ -172,8 +173,10 @@ struct Query {
     int x0 = ix - kx, x1 = ix + kx;
     if (!chord(g, b2, g2, x0, x1)) return;
     const uint32_t lin = ((uint32_t)(iz + dz) * (uint32_t)g.dy + (uint32_t)(iy + dy)) * (uint32_t)g.dx;
+    PCD_DASSERT(x0 >= 0 && x1 < g.dx && (uint64_t)lin + (uint64_t)x1 + 1 <= (uint64_t)g.dx * g.dy * g.dz);
     const uint32_t b = __ldg(&g.cell_start[lin + x0]);
     const uint32_t e = __ldg(&g.cell_start[lin + x1 + 1]);
+    PCD_DASSERT(b <= e && e <= g.n);
     scan(g, b, e, 0, 1);
   }
 
@@ -272,7 +275,9 @@ struct FarSearch {
     int x0 = cxc * g.xs, x1 = x0 + g.xs - 1;
     if (!Q.chord(g, b2, g2, x0, x1)) return;
     const uint32_t lin = ((uint32_t)cz * (uint32_t)g.dy + (uint32_t)cy) * (uint32_t)g.dx;
+    PCD_DASSERT(x0 >= 0 && x1 < g.dx && cy >= 0 && cy < g.dy && cz >= 0 && cz < g.dz);
     const uint32_t b = __ldg(&g.cell_start[lin + x0]), e = __ldg(&g.cell_start[lin + x1 + 1]);
+    PCD_DASSERT(b <= e && e <= g.n);
     if (b == e) return;
     Q.scan(g, b, e, lane, G);
     Q.best = min_u64(Q.best);
@@ -331,6 +336,7 @@ struct FarSearch {
     unsigned long long w = 0;
     if (in_grid) {
       lb = block_lb2(X, Y, Z);
+      PCD_DASSERT(X >= 0 && X < g.nbx && Y >= 0 && Y < g.nby && Z >= 0 && Z < g.nbz);
       if (lb <= b2) w = __ldg(&g.occ[((int64_t)Z * g.nby + Y) * g.nbx + X]);
     }
     visit(w != 0, X, Y, Z, w, lb);
@@ -455,6 +461,7 @@ __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridVie
     base = __shfl_sync(act, base, leader);
     if (!resolved) {
       FarItem it; it.best = Q.best; it.i = i; it.pad = 0; it.rec = Q.record();
+      PCD_DASSERT((int64_t)base + __popc(m) <= n);                  // the queue holds one entry per query at most
       far[base + __popc(m & ((1u << lane) - 1u))] = it;
     }
   }
@@ -479,6 +486,7 @@ __global__ void __launch_bounds__(NN_THREADS, FAR_MIN_BLOCKS) k_nn_far(GridView 
     for (unsigned e = e0; e < e1; e++) {
       const uint4 c0 = __ldg(&fq[2 * (size_t)e]), c1 = __ldg(&fq[2 * (size_t)e + 1]);
       const uint32_t i = c0.z;
+      PCD_DASSERT(e < count);
       Query Q;
       Q.from_record(g, make_float4(__uint_as_float(c1.x), __uint_as_float(c1.y), __uint_as_float(c1.z), __uint_as_float(c1.w)));
       Q.best = ((unsigned long long)c0.y << 32) | c0.x;

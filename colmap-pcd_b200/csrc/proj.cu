@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
   for (int64_t s = warp; s < sm.n_seg; s += nwarps) {
     const uint2 sg = __ldg(&sm.seg[s]);
     const int64_t c = sg.x;
+    PCD_DASSERT(c >= 0 && c < sm.n_cells && sg.y >= sm.start[c] && sg.y < sm.start[c + 1]);
     // a11: cell centre (idx*len, idy*height, idz*width) against the five planes, float32, left to right
     float x = (float)sm.keys[3 * c] * sm.len, y = (float)sm.keys[3 * c + 1] * sm.height, z = (float)sm.keys[3 * c + 2] * sm.width;
     bool in = true;
@@ -181,8 +182,9 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
           const int W = a1 - a0 + 1, tot = W * (r1 - r0 + 1);
           for (int t = lane; t < tot; t += 32) {
             const int dv = t / W, du = t - dv * W;
+            PCD_DASSERT(r0 + dv >= 0 && r0 + dv < P.h && a0 + du >= 0 && a0 + du < P.w);
             unsigned long long* px = zbuf + (int64_t)(r0 + dv) * P.w + (a0 + du);
-            if (pk < *px) atomicMin(px, pk);
+            if (pk < *px) atomicMin(px, pk);               // plain pre-read: a stale value is never below the true one (values only fall)
           }
         }
       } else if (rect) {
@@ -200,6 +202,7 @@ __global__ void __launch_bounds__(256) k_project(SubmapView sm, ImgParams P, con
               uint32_t bits = __ldg(&mask[(int64_t)v * P.words + wd]) & m;
               while (bits) {
                 int bpos = __ffs(bits) - 1; bits &= bits - 1;
+                PCD_DASSERT(v >= 0 && v < P.h && (wd << 5) + bpos >= 0 && (wd << 5) + bpos < P.w);
                 unsigned long long* px = zbuf + (int64_t)v * P.w + (wd << 5) + bpos;
                 if (packed < *px) atomicMin(px, packed);
               }
@@ -233,7 +236,7 @@ __global__ void k_atomic_sweep(unsigned long long* __restrict__ buf, int64_t wor
   }
 }
 
-__global__ void k_gather_winners(const int64_t* __restrict__ px, int64_t n, const unsigned long long* __restrict__ zbuf,
+__global__ void k_gather_winners(const int64_t* __restrict__ px, int64_t n, const unsigned long long* __restrict__ zbuf, int64_t npx,
                                  int32_t* __restrict__ widx, float* __restrict__ wrange, unsigned long long* __restrict__ stats) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   bool hit = false;
@@ -241,6 +244,7 @@ __global__ void k_gather_winners(const int64_t* __restrict__ px, int64_t n, cons
     int32_t idx = -1; float r = INFINITY;
     int64_t p = px[i];
     if (p >= 0) {
+      PCD_DASSERT(p < npx);
       unsigned long long z = zbuf[p];
       if (z != ~0ull) { idx = (int32_t)(uint32_t)(z & 0xffffffffu); r = __uint_as_float((unsigned)(z >> 32)); hit = true; }
     }
@@ -305,7 +309,7 @@ static int project_one(pcd_cloud* c, const pcd_image* img, const double coef[4],
     PCD_LAUNCH_CHECK(ctx);
   }
   if (n_feat > 0 && d_widx) {
-    k_gather_winners<<<pcd_blocks(n_feat, 256), 256, 0, st>>>(d_px, n_feat, zb, d_widx, d_wrange, d_stats);
+    k_gather_winners<<<pcd_blocks(n_feat, 256), 256, 0, st>>>(d_px, n_feat, zb, npx, d_widx, d_wrange, d_stats);
     PCD_LAUNCH_CHECK(ctx);
   }
   if (zbuf_out) *zbuf_out = zb;

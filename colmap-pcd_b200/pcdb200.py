@@ -10,7 +10,7 @@ import weakref
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpcd_b200.so")
+LIB_PATH = os.environ.get("PCD_B200_LIB") or os.path.join(_HERE, "libpcd_b200.so")      # PCD_B200_LIB: another build of the same library (make dbg)
 
 K_NN_KEYSORT, K_NN_SEARCH, K_ASSOC_RECORD, K_RESJAC, K_PROJECT, K_NN_FAR = 0, 1, 2, 3, 4, 5
 TYPE_PROJ, TYPE_ICP, TYPE_ICP_GROUND, TYPE_NONE = 0, 1, 2, 255

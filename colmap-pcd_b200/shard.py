@@ -120,7 +120,10 @@ class PeerExchange:
     address space).  After a pass, a rank pushes its r [Q] and J [Q, 3] blocks straight into its slot of every peer's
     buffer with device-to-device copies on per-peer side streams -- copy engines over NVLink / NVSwitch, no SM taken
     from the search kernels that run the next pass at the same time -- then joins a signal-pad barrier, after which
-    every rank holds every block.  Two receive buffers alternate, so a consumer has a whole pass to read one.
+    every rank holds every block.  Two receive buffers alternate.  Ordering between passes: the pushes of pass k + 2
+    into receive buffer b wait for the event recorded behind the barrier of pass k + 1, i.e. until EVERY rank has
+    entered start(k + 1); a consumer must therefore enqueue its reads of pass k (wait_buffer / wait, then its kernels)
+    BEFORE it calls start(k + 1) -- after that call the buffer of pass k may be overwritten by a faster peer.
     The fp64 statistics still go through a (tiny) NCCL all-reduce.
     wire = "f32": the blocks are first rounded to float4 {r, J0, J1, J2} by `pack` (see Exchange) and one 16 B/query
     copy per peer replaces the two fp64 ones.
@@ -152,6 +155,7 @@ class PeerExchange:
         self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(self.world)]
         self.events = [torch.cuda.Event() for _ in range(2)]
         self.pending = [False, False]
+        self.recorded = [False, False]
         self.last = 0
 
     def views(self, buf):
@@ -175,6 +179,8 @@ class PeerExchange:
             p = (me + k) % self.world
             st = self.streams[p]
             st.wait_stream(src)
+            if self.recorded[1 - buf]:
+                st.wait_event(self.events[1 - buf])      # every rank is past the barrier of the previous pass
             with torch.cuda.stream(st):
                 dst = self.peer_views[buf][p]
                 if self.wire == "f32":
@@ -191,6 +197,7 @@ class PeerExchange:
             dist.all_reduce(self.stats, op=dist.ReduceOp.SUM, group=self.group)
             self.events[buf].record(self.main)
         self.pending[buf] = True
+        self.recorded[buf] = True
         self.last = buf
 
     def wait_buffer(self, buf):
