@@ -222,7 +222,9 @@ int pcd_group_associate_evaluate_batch(pcd_group_cloud* gc, const double* p_xyz,
   std::vector<int> rc((size_t)G, PCD_OK);
   std::vector<double> sums((size_t)G, 0.0);
   std::vector<std::thread> th;
-  for (int k = 0; k < G; k++) {
+  bool spawn_failed = false;
+  for (int k = 0; k < G && !spawn_failed; k++) {
+    try {
     th.emplace_back([&, k]() {
       int64_t lo, hi;
       pcd::shard_bounds(n, G, k, &lo, &hi);
@@ -246,8 +248,10 @@ int pcd_group_associate_evaluate_batch(pcd_group_cloud* gc, const double* p_xyz,
         rc[(size_t)k] = pcd_associate_batch(gc->c[(size_t)k], p_xyz + 3 * lo, range ? range + lo : nullptr, opt_num ? opt_num + lo : nullptr,
                                             sweep, m, variant, &o);
     });
+    } catch (...) { spawn_failed = true; }             // no exception crosses the C ABI
   }
   for (auto& t : th) t.join();
+  if (spawn_failed) { gc->g->err = "could not start a host thread per device"; return PCD_E_NOMEM; }
   for (int k = 0; k < G; k++)
     if (rc[(size_t)k]) { gc->g->err = pcd_last_error(gc->c[(size_t)k]->ctx); return rc[(size_t)k]; }
   if (sum_sq) { double t = 0.0; for (double s : sums) t += s; *sum_sq = t; }      // rank order: deterministic
@@ -262,7 +266,9 @@ int pcd_group_project_images(pcd_group_cloud* gc, const pcd_image* imgs, int64_t
   std::vector<int> rc((size_t)G, PCD_OK);
   std::vector<std::vector<int64_t>> st((size_t)G, std::vector<int64_t>(4, 0));
   std::vector<std::thread> th;
-  for (int k = 0; k < G; k++) {
+  bool spawn_failed = false;
+  for (int k = 0; k < G && !spawn_failed; k++) {
+    try {
     th.emplace_back([&, k]() {
       int64_t lo, hi;
       pcd::shard_bounds(n_img, G, k, &lo, &hi);
@@ -274,8 +280,10 @@ int pcd_group_project_images(pcd_group_cloud* gc, const pcd_image* imgs, int64_t
       rc[(size_t)k] = pcd_project_images(gc->c[(size_t)k], imgs + lo, hi - lo, coef, feat_xy ? feat_xy + 2 * f0 : nullptr, fs.data(),
                                          winner_idx ? winner_idx + f0 : nullptr, winner_range ? winner_range + f0 : nullptr, st[(size_t)k].data());
     });
+    } catch (...) { spawn_failed = true; }
   }
   for (auto& t : th) t.join();
+  if (spawn_failed) { gc->g->err = "could not start a host thread per device"; return PCD_E_NOMEM; }
   for (int k = 0; k < G; k++)
     if (rc[(size_t)k]) { gc->g->err = pcd_last_error(gc->c[(size_t)k]->ctx); return rc[(size_t)k]; }
   if (stats) for (int i = 0; i < 4; i++) { stats[i] = 0; for (int k = 0; k < G; k++) stats[i] += st[(size_t)k][(size_t)i]; }

@@ -183,6 +183,16 @@ class Context:
                                                    C.c_double(max_icp), _ptr(e), C.byref(cnt)), "pcd_filter_outliers_batch")
         return e, cnt.value
 
+    def lidar_point_ops(self, xyz, abcd, pt=None, normalize=True):
+        """pcd_lidar_point_ops: (abcd_out, ComputeDist, ComputePointToPointDist, ComputeAngle) of n records."""
+        xyz, abcd = _f64(xyz, 3), _f64(abcd, 4)
+        n = len(xyz)
+        p = None if pt is None else _f64(pt, 3)
+        out = np.empty((n, 4)); dp = np.empty(n); dd = np.empty(n); an = np.empty(n)
+        self.check(lib().pcd_lidar_point_ops(self._h, _ptr(xyz), _ptr(abcd), _ptr(p), C.c_int64(n), C.c_int(int(normalize)), _ptr(out),
+                                             _ptr(dp), _ptr(dd), _ptr(an)), "pcd_lidar_point_ops")
+        return out, dp, dd, an
+
     def match_proj(self, p, cand, cand_start):
         p, cand = _f64(p, 3), _f64(cand, 6)
         cs = np.ascontiguousarray(cand_start, dtype=np.int64)
