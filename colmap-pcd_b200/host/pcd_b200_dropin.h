@@ -6,9 +6,12 @@
 //   colmap::lidar::Kdtree                               src/lidar/kdtree.h:13-22, kdtree.cc:5-21
 //   colmap::lidar::PcdProjectionOptions / PcdProj       src/lidar/pcd_projection.h:31-66
 //   colmap::lidar::PointCloudProcess                    src/lidar/ply.h:13-40, ply.cc:9-107
-//   colmap::LidarPoint (the match record)               src/lidar/lidar_point.h:9-52
+//   colmap::LidarPoint (the match record, full interface) src/lidar/lidar_point.h:9-52, lidar_point.cc:5-50
 //   colmap::BundleAdjustmentLidarCostFunction::Create   src/base/cost_functions.h:180-232
-//   colmap::LidarEvaluationCallback                     (new: the ceres::EvaluationCallback of SURVEY 8b)
+//   colmap::LidarEvaluationBatch / LidarEvaluationCallback (new: the ceres::EvaluationCallback of SURVEY 8b, one batch per problem)
+//   colmap::MatchClosestLidarPoints                     (new: the three serial association loops as one batched call)
+//   colmap::Project2Image                               (new: src/optim/bundle_adjustment.cc:241-281 for all variable points at once)
+// Several GPUs: PCD_B200_DEVICES="0,1,..." or DropinRuntime::SetDevices() shards the batched calls over pcd_group_*.
 //
 // Inside the reference tree define PCD_DROPIN_WITH_EIGEN / PCD_DROPIN_WITH_CERES before including
 // this header: the real Eigen and Ceres types are then used.  Without them (this repository's own
