@@ -337,6 +337,64 @@ int main(int argc, char** argv) {
       const size_t np = Project2Image(pcp, &rec, pids, 7u, 30, cache2);
       if (np != 1 || cache2.size() != 2 || !same(cache2[9], m2)) { fprintf(stderr, "Project2Image selected %zu images\n", np); return 1; }
     }
+    // (6) MatchVariablePoint2LidarPoint (src/optim/bundle_adjustment.cc:288-350): the reference body, transcribed, per
+    // point over the shim's LidarPoint -- against the batched MatchVariablePoints2LidarPoints
+    {
+      struct El { uint32_t image_id; };
+      struct TrackT { std::vector<El> e; const std::vector<El>& Elements() const { return e; } };
+      struct P3 { TrackT t; Eigen::Vector3d xyz; const TrackT& Track() const { return t; } Eigen::Vector3d XYZ() const { return xyz; } };
+      struct Recon { std::map<uint64_t, P3> pts; P3& Point3D(uint64_t id) { return pts[id]; } } rec;
+      std::map<uint64_t, std::map<uint64_t, Eigen::Vector6d>> lidar_searched_image_ids_;
+      lidar_searched_image_ids_[7] = m; lidar_searched_image_ids_[9] = m2;
+      std::vector<uint64_t> pids;
+      for (auto& kv : m) {                     // feature ids seen in image 7; most are in image 9 as well
+        P3 p3; p3.t.e = {{9}, {5}, {7}};
+        for (int c = 0; c < 3; c++) p3.xyz(c) = kv.second(c) + 0.03 * (double)((kv.first + (uint64_t)c) % 5) - 0.05;
+        rec.pts[kv.first] = p3; pids.push_back(kv.first);
+        if (pids.size() >= 300) break;
+      }
+      std::map<uint64_t, LidarPoint> serial, batched;
+      for (uint64_t point3D_id : pids) {
+        P3& point3D = rec.Point3D(point3D_id);
+        Eigen::Vector3d pt_xyz = point3D.XYZ();
+        double angle = 360;
+        Eigen::Vector6d lidar_pt;
+        const auto& track_els = point3D.Track().Elements();
+        for (auto& track_el : track_els){
+          auto iter = lidar_searched_image_ids_.find(track_el.image_id);
+          if (iter == lidar_searched_image_ids_.end()) continue;
+          auto lidar_pt_ptr = iter->second.find(point3D_id);
+          if (lidar_pt_ptr != iter->second.end()){
+            Eigen::Vector6d lidar_pt_temp = lidar_pt_ptr->second;
+            Eigen::Vector3d norm = lidar_pt_temp.block(3,0,3,1);
+            Eigen::Vector3d vec = pt_xyz - lidar_pt_temp.block(0,0,3,1);
+            double angle_temp = std::abs(vec.dot(norm)/(norm.norm()*vec.norm()));
+            if (angle_temp < angle){
+              angle = angle_temp;
+              lidar_pt = lidar_pt_temp;
+            }
+          }
+        }
+        if (angle != 360){
+          Eigen::Vector3d norm = lidar_pt.block(3,0,3,1);
+          Eigen::Vector3d l_pt = lidar_pt.block(0,0,3,1);
+          double d = 0 - l_pt.dot(norm);
+          Eigen::Vector4d plane;
+          plane << norm(0),norm(1),norm(2),d;
+
+          LidarPoint lidar_point(LidarPointType::Proj,l_pt,plane);
+          lidar_point.SetDist( lidar_point.ComputeDist(pt_xyz));
+          lidar_point.SetAngle( lidar_point.ComputeAngle(pt_xyz));
+          Eigen::Vector3ub color;
+          color << 255,0,0;
+          lidar_point.SetColor(color);
+          serial.insert({point3D_id,lidar_point});
+        }
+      }
+      if (!MatchVariablePoints2LidarPoints(&rec, pids, lidar_searched_image_ids_, &batched)) { fprintf(stderr, "batched a17 failed\n"); return 1; }
+      if (serial.size() < 50 || !SameRecords(serial, batched, true, "MatchVariablePoint2LidarPoint")) return 1;
+      for (auto& kv : batched) if (kv.second.Type() != LidarPointType::Proj) { fprintf(stderr, "a17 type\n"); return 1; }
+    }
     // (4) the initial-pair overload (src/lidar/pcd_projection.cc:102-220): one push_back per keypoint after what the vector held
     std::vector<std::pair<Eigen::Vector2d, bool>> pt_xys;
     for (int64_t i = 0; i < nf; i++) pt_xys.push_back({Eigen::Vector2d{im[18 + 2 * i], im[19 + 2 * i]}, false});

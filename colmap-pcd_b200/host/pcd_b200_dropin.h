@@ -51,7 +51,10 @@ template <typename T, int N> struct PcdVec {
   const T* data() const { return v; }
   // the few Eigen operations the reference's association loops spell out (block(i,0,3,1), a.dot(b), v << a,b,c,d)
   PcdVec<T, 3> block(int i, int, int, int) const { PcdVec<T, 3> r; for (int k = 0; k < 3; k++) r.v[k] = v[i + k]; return r; }
-  T dot(const PcdVec& o) const { T s = T(0); for (int k = 0; k < N; k++) s += v[k] * o.v[k]; return s; }
+  // three-element reductions in Eigen's order, a0 + (a1 + a2) (Redux.h splits at Length / 2)
+  T dot(const PcdVec& o) const { if (N == 3) return v[0] * o.v[0] + (v[1] * o.v[1] + v[2] * o.v[2]); T s = T(0); for (int k = 0; k < N; k++) s += v[k] * o.v[k]; return s; }
+  T norm() const { return std::sqrt(dot(*this)); }
+  PcdVec operator-(const PcdVec& o) const { PcdVec r; for (int k = 0; k < N; k++) r.v[k] = v[k] - o.v[k]; return r; }
   struct Comma {
     PcdVec* m; int i;
     Comma operator,(T x) { if (i < N) m->v[i] = x; return Comma{m, i + 1}; }
@@ -481,6 +484,15 @@ class LidarPoint {
     if (o.angle) p.angle_ = o.angle[i];
     return p;
   }
+  static LidarPoint FromFields(LidarPointType type, const double xyz[3], const double abcd[4], double dist, double angle, uint8_t r, uint8_t g, uint8_t b) {
+    LidarPoint p;
+    p.type_ = type;
+    for (int k = 0; k < 3; k++) p.xyz_(k) = xyz[k];
+    for (int k = 0; k < 4; k++) p.abcd_(k) = abcd[k];
+    p.dist_ = dist; p.angle_ = angle;
+    p.color_(0) = r; p.color_(1) = g; p.color_(2) = b;
+    return p;
+  }
   void SetType(LidarPointType type) { type_ = type; }
   void SetColor(Eigen::Vector3ub& color) { color_ = color; }
   void SetDist(const double& dist) { dist_ = dist; }
@@ -552,6 +564,44 @@ inline size_t Project2Image(lidar::PointCloudProcess& pcp, ReconstructionT* reco
   }
   pcp.pcd_proj_->template SetNewImages<ImageT, CameraT>(images, cameras, ids, lidar_searched_image_ids_);
   return todo.size();
+}
+
+// BundleAdjustmentConfig::MatchVariablePoint2LidarPoint (src/optim/bundle_adjustment.cc:288-350) for many points at once:
+// per point the candidates are the projected lidar points its track's cached images hold for it, in track order; the
+// kernel keeps the one with the smallest |v . n| / (|n| |v|) (strict <, start value 360) and builds the Proj record
+// (Normalize, dist = ComputeDist, angle = ComputeAngle; colour 255,0,0 as :343-345).
+template <typename ReconstructionT, typename PointIds, typename CacheT>
+inline bool MatchVariablePoints2LidarPoints(ReconstructionT* reconstruction, const PointIds& point3D_ids,
+                                            const CacheT& lidar_searched_image_ids_, std::map<uint64_t, LidarPoint>* out) {
+  std::vector<double> p, cand; std::vector<int64_t> start(1, 0); std::vector<uint64_t> ids;
+  for (const auto point3D_id : point3D_ids) {
+    auto& point3D = reconstruction->Point3D(point3D_id);
+    const auto xyz = point3D.XYZ();
+    for (int k = 0; k < 3; k++) p.push_back(xyz(k));
+    for (const auto& track_el : point3D.Track().Elements()) {
+      auto iter = lidar_searched_image_ids_.find(track_el.image_id);
+      if (iter == lidar_searched_image_ids_.end()) continue;
+      auto lidar_pt_ptr = iter->second.find(point3D_id);
+      if (lidar_pt_ptr == iter->second.end()) continue;
+      for (int k = 0; k < 6; k++) cand.push_back(lidar_pt_ptr->second(k));
+    }
+    start.push_back((int64_t)cand.size() / 6); ids.push_back((uint64_t)point3D_id);
+  }
+  const int64_t n = (int64_t)ids.size();
+  if (n == 0) return true;
+  std::vector<uint8_t> found((size_t)n); std::vector<double> xyz(3 * (size_t)n), abcd(4 * (size_t)n), dist((size_t)n), angle((size_t)n);
+  lidar::DropinRuntime& rt = lidar::DropinRuntime::Get();
+  if (!rt.Ensure()) return false;
+  {
+    std::lock_guard<std::mutex> g(rt.mu);
+    if (pcd_match_proj_batch(rt.ctx, p.data(), cand.data(), start.data(), n, found.data(), xyz.data(), abcd.data(), dist.data(), angle.data()) != PCD_OK) {
+      rt.error = pcd_last_error(rt.ctx); return false;
+    }
+  }
+  for (int64_t i = 0; i < n; i++)
+    if (found[(size_t)i])
+      out->insert({ids[(size_t)i], LidarPoint::FromFields(LidarPointType::Proj, &xyz[3 * (size_t)i], &abcd[4 * (size_t)i], dist[(size_t)i], angle[(size_t)i], 255, 0, 0)});
+  return true;
 }
 
 // Batched replacement of the three serial association loops (src/sfm/incremental_mapper.cc:1138-1166,
