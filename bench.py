@@ -67,7 +67,9 @@ def parse_args():
                     help="N>1: format of the residual/Jacobian blocks on the wire. f64 (default): as computed, 32 B/query. "
                          "f32: rounded to a float4 by pcd_pack_blocks_f32_dev first, 16 B/query (relative error <= 2^-24, "
                          "stated separately from the fp64 result)")
-    ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather", "p2p"],
+    ap.add_argument("--p2p-chunks", type=int, default=1, help="--exchange p2p / hybrid: pieces per peer copy, each on a stream of its own")
+    ap.add_argument("--hybrid-nccl-frac", type=float, default=0.45, help="--exchange hybrid: share of the rows that travels by NCCL")
+    ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather", "p2p", "hybrid"],
                     help="N > 1: NCCL all-gather of the r / J blocks to every rank, NCCL gather to rank 0, or p2p: pushes into "
                          "every peer's symmetric buffer by copy engines over NVLink")
     ap.add_argument("--e2e-record", default="slim", choices=["slim", "full"],
@@ -184,6 +186,9 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
                        "l2": "inputs exceed L2 (no flush needed)" if q_per_gpu * 24 > 126e6 * 2 else "L2 flushed between steps",
                        "parallelism": f"queries sharded x{world}, cloud+index replicated",
                        "exchange": "none (1 GPU)" if world == 1 else
+                       (f"per pass: rows [0, {args.hybrid_nccl_frac:.2f} Q) of the fp64 r, J blocks by NCCL all_gather, the rest by copy-engine pushes into "
+                        f"every peer's symmetric-memory buffer ({args.p2p_chunks} piece(s) per peer), + all_reduce of sum r^2; side streams overlapping the next pass")
+                       if args.exchange == "hybrid" else
                        (f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J "
                         f"{'fp64 blocks (32 B/query)' if args.exchange_wire == 'f64' else 'blocks rounded to float4 by k_pack_blocks_f32 (16 B/query; fp64 results stay on the producer)'} + "
                         "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass") if args.exchange != "p2p" else
@@ -472,7 +477,9 @@ def run_b200(args):
         def pack(r_, J_, out, st):
             ctx.pack_blocks_f32_dev(r_.data_ptr(), J_.data_ptr(), Q, out.data_ptr(), st)
         if args.exchange == "p2p":
-            gather = shard.PeerExchange(Q, dev, wire=args.exchange_wire, pack=pack if args.exchange_wire == "f32" else None)
+            gather = shard.PeerExchange(Q, dev, wire=args.exchange_wire, pack=pack if args.exchange_wire == "f32" else None, chunks=args.p2p_chunks)
+        elif args.exchange == "hybrid":
+            gather = shard.HybridExchange(Q, dev, nccl_frac=args.hybrid_nccl_frac, chunks=args.p2p_chunks)
         else:
             gather = shard.Exchange(Q, dev, root=0 if args.exchange == "gather" else None, wire=args.exchange_wire,
                                     pack=pack if args.exchange_wire == "f32" else None)

@@ -129,11 +129,14 @@ class PeerExchange:
     copy per peer replaces the two fp64 ones.
     """
 
-    def __init__(self, q_per_rank, device, group=None, wire="f64", pack=None):
+    def __init__(self, q_per_rank, device, group=None, wire="f64", pack=None, chunks=1):
+        """chunks > 1: every peer's copy is cut into that many pieces issued on streams of their own (more copies in
+        flight per peer)."""
         import torch.distributed._symmetric_memory as symm
         if wire not in ("f64", "f32") or (wire == "f32" and pack is None):
             raise ValueError("PeerExchange: wire is 'f64' or 'f32' (the latter needs the pack callable)")
         self.wire, self.pack = wire, pack
+        self.chunks = max(1, int(chunks))
         self.group = group if group is not None else dist.group.WORLD
         self.world = dist.get_world_size(self.group)
         self.rank = dist.get_rank(self.group)
@@ -152,7 +155,7 @@ class PeerExchange:
             self.pack_stream = torch.cuda.Stream(device=dev, priority=-1)
         self.stats = torch.zeros(3, dtype=torch.float64, device=dev)
         self.main = torch.cuda.Stream(device=dev, priority=-1)
-        self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(self.world)]
+        self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(self.world * self.chunks)]
         self.events = [torch.cuda.Event() for _ in range(2)]
         self.pending = [False, False]
         self.recorded = [False, False]
@@ -175,19 +178,22 @@ class PeerExchange:
                 self.pack(r, J, self.w_local[buf], self.pack_stream.cuda_stream)
             src, wf = self.pack_stream, self.w_local[buf].reshape(-1)
         Jf = J.reshape(-1)
+        C = self.chunks
         for k in range(self.world):                      # own slot first, then the peers in ring order
             p = (me + k) % self.world
-            st = self.streams[p]
-            st.wait_stream(src)
-            if self.recorded[1 - buf]:
-                st.wait_event(self.events[1 - buf])      # every rank is past the barrier of the previous pass
-            with torch.cuda.stream(st):
-                dst = self.peer_views[buf][p]
-                if self.wire == "f32":
-                    dst[4 * me * q:4 * (me + 1) * q].copy_(wf, non_blocking=True)
-                else:
-                    dst[me * q:(me + 1) * q].copy_(r, non_blocking=True)
-                    dst[n + 3 * me * q:n + 3 * (me + 1) * q].copy_(Jf, non_blocking=True)
+            for c in range(C):
+                a, b = q * c // C, q * (c + 1) // C      # this piece's rows
+                st = self.streams[p * C + c]
+                st.wait_stream(src)
+                if self.recorded[1 - buf]:
+                    st.wait_event(self.events[1 - buf])  # every rank is past the barrier of the previous pass
+                with torch.cuda.stream(st):
+                    dst = self.peer_views[buf][p]
+                    if self.wire == "f32":
+                        dst[4 * (me * q + a):4 * (me * q + b)].copy_(wf[4 * a:4 * b], non_blocking=True)
+                    else:
+                        dst[me * q + a:me * q + b].copy_(r[a:b], non_blocking=True)
+                        dst[n + 3 * (me * q + a):n + 3 * (me * q + b)].copy_(Jf[3 * a:3 * b], non_blocking=True)
         self.main.wait_stream(cur)
         for st in self.streams:
             self.main.wait_stream(st)
@@ -209,6 +215,35 @@ class PeerExchange:
         torch.cuda.current_stream().wait_stream(self.main)
         r_all, J_all = self.views(self.last)
         return r_all, J_all, self.stats
+
+
+class HybridExchange:
+    """Rows [0, split) of every rank's blocks travel by NCCL all-gather (its CTAs capped by NCCL_MAX_CTAS so that the
+    search kernels keep their SMs), rows [split, Q) by copy-engine pushes into symmetric memory: the two paths use
+    different hardware (SMs + NVLink vs copy engines + NVLink) and run side by side.  fp64 blocks on both."""
+
+    def __init__(self, q_per_rank, device, group=None, nccl_frac=0.45, chunks=1):
+        self.q = int(q_per_rank)
+        self.split = max(1, min(self.q - 1, int(self.q * float(nccl_frac))))
+        self.a = Exchange(self.split, device, group=group, root=None)
+        self.b = PeerExchange(self.q - self.split, device, group=group, chunks=chunks)
+        self.world = self.a.world
+
+    def start(self, r, J, stats, buf=0):
+        s = self.split
+        self.a.start(r[:s], J[:s], stats, buf)
+        self.b.start(r[s:], J[s:], stats, buf)
+
+    def wait_buffer(self, buf):
+        self.a.wait_buffer(buf); self.b.wait_buffer(buf)
+
+    def wait(self):
+        ra, Ja, st = self.a.wait()
+        rb, Jb, _ = self.b.wait()
+        s, q, w = self.split, self.q, self.world
+        r_all = torch.cat([torch.cat([ra[k * s:(k + 1) * s], rb[k * (q - s):(k + 1) * (q - s)]]) for k in range(w)])
+        J_all = torch.cat([torch.cat([Ja[k * s:(k + 1) * s], Jb[k * (q - s):(k + 1) * (q - s)]]) for k in range(w)])
+        return r_all, J_all, st
 
 
 def gather_ragged(local, group=None):
