@@ -67,11 +67,13 @@ def parse_args():
                     help="N>1: format of the residual/Jacobian blocks on the wire. f64 (default): as computed, 32 B/query. "
                          "f32: rounded to a float4 by pcd_pack_blocks_f32_dev first, 16 B/query (relative error <= 2^-24, "
                          "stated separately from the fp64 result)")
-    ap.add_argument("--p2p-chunks", type=int, default=1, help="--exchange p2p / hybrid: pieces per peer copy, each on a stream of its own")
+    ap.add_argument("--p2p-chunks", type=int, default=4, help="--exchange auto / p2p / hybrid: pieces per peer copy, each on a stream of its own "
+                    "(measured at 8 GPUs: 1 -> 8.4 ms per pass, 4 -> 6.1, 8 -> 6.3, 16 -> 10.0)")
     ap.add_argument("--hybrid-nccl-frac", type=float, default=0.45, help="--exchange hybrid: share of the rows that travels by NCCL")
-    ap.add_argument("--exchange", default="allgather", choices=["gather", "allgather", "p2p", "hybrid"],
-                    help="N > 1: NCCL all-gather of the r / J blocks to every rank, NCCL gather to rank 0, or p2p: pushes into "
-                         "every peer's symmetric buffer by copy engines over NVLink")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "gather", "allgather", "p2p", "hybrid"],
+                    help="N > 1: auto = p2p when symmetric memory can be set up, else allgather (the line's exchange_used says which); "
+                         "allgather / gather: NCCL all-gather of the r / J blocks to every rank / gather to rank 0; p2p: pushes into "
+                         "every peer's symmetric buffer by copy engines over NVLink; hybrid: NCCL for a share of the rows, copy engines for the rest")
     ap.add_argument("--e2e-record", default="slim", choices=["slim", "full"],
                     help="fields the end-to-end leg copies back: slim = idx, accepted, type, abcd + r, J (70 B/query: the caller holds the "
                          "cloud, xyz and dist follow from idx); full = the whole LidarPoint record as in round 1 (+ xyz, dist: 102 B/query)")
@@ -191,9 +193,10 @@ def base_line(args, n_cloud, q_per_gpu, desc, world):
                        if args.exchange == "hybrid" else
                        (f"per pass: {'gather to rank 0' if args.exchange == 'gather' else 'all_gather'} of r and J "
                         f"{'fp64 blocks (32 B/query)' if args.exchange_wire == 'f64' else 'blocks rounded to float4 by k_pack_blocks_f32 (16 B/query; fp64 results stay on the producer)'} + "
-                        "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass") if args.exchange != "p2p" else
+                        "all_reduce of sum r^2, NCCL on a high-priority side stream overlapping the next pass") if args.exchange not in ("p2p", "auto") else
                        (f"per pass: r and J {'fp64 blocks (32 B/query)' if args.exchange_wire == 'f64' else 'blocks rounded to float4 (16 B/query)'} pushed into every peer's symmetric-memory buffer by copy engines over "
-                        "NVLink + signal barrier + all_reduce of sum r^2, on side streams overlapping the next pass")}}
+                        f"NVLink, {args.p2p_chunks} piece(s) per peer" + ("" if args.exchange == "p2p" else " (auto: NCCL all_gather instead when symmetric memory cannot be set up)") +
+                        " + signal barrier + all_reduce of sum r^2, on side streams overlapping the next pass")}}
 
 
 def cpu_pass(orc, tree, q, rng, threads):
@@ -473,11 +476,24 @@ def run_b200(args):
     d_sumb = [d_sum, torch.zeros_like(d_sum)] if world > 1 else [d_sum]     # sum r^2 travels with its pass's blocks
     shard = load_shard()
     gather = None
+    exchange_used = args.exchange if world > 1 else "none"
     if world > 1:
         def pack(r_, J_, out, st):
             ctx.pack_blocks_f32_dev(r_.data_ptr(), J_.data_ptr(), Q, out.data_ptr(), st)
-        if args.exchange == "p2p":
-            gather = shard.PeerExchange(Q, dev, wire=args.exchange_wire, pack=pack if args.exchange_wire == "f32" else None, chunks=args.p2p_chunks)
+        if args.exchange in ("p2p", "auto"):
+            ok = torch.ones(1, dtype=torch.int32, device=dev)
+            try:
+                gather = shard.PeerExchange(Q, dev, wire=args.exchange_wire, pack=pack if args.exchange_wire == "f32" else None, chunks=args.p2p_chunks)
+            except Exception as ex:                       # no symmetric memory on this box / build
+                if args.exchange == "p2p":
+                    raise
+                print(f"bench.py: rank {rank}: symmetric-memory exchange unavailable ({ex}); using the NCCL all-gather", file=sys.stderr)
+                ok.zero_(); gather = None
+            if args.exchange == "auto":
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # every rank must take the same path
+                if int(ok.item()) == 0:
+                    gather = shard.Exchange(Q, dev, root=None, wire=args.exchange_wire, pack=pack if args.exchange_wire == "f32" else None)
+            exchange_used = "p2p" if isinstance(gather, shard.PeerExchange) else "allgather"
         elif args.exchange == "hybrid":
             gather = shard.HybridExchange(Q, dev, nccl_frac=args.hybrid_nccl_frac, chunks=args.p2p_chunks)
         else:
@@ -630,6 +646,7 @@ def run_b200(args):
         achieved = ALG_BYTES_NN * Q / nn_avg_s / 1e9
         if exchange_ok is not None:
             line["exchange_verified"] = exchange_ok
+            line["exchange_used"] = exchange_used
         line.update({"value": passes * Q * world / (ms_step * 1e-3), "ms_per_step": ms_step, "gpu_launches": int(launches),
                      "clocks": clocks,
                      "e2e": None if args.no_e2e else {"value": Q * world * e2e_steps / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": int(h2d),
