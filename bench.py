@@ -68,7 +68,7 @@ def parse_args():
                          "f32: rounded to a float4 by pcd_pack_blocks_f32_dev first, 16 B/query (relative error <= 2^-24, "
                          "stated separately from the fp64 result)")
     ap.add_argument("--p2p-chunks", type=int, default=4, help="--exchange auto / p2p / hybrid: pieces per peer copy, each on a stream of its own "
-                    "(measured at 8 GPUs: 1 -> 8.4 ms per pass, 4 -> 6.1, 8 -> 6.3, 16 -> 10.0)")
+                    "(measured at 8 GPUs: 1 -> 8.4 ms per pass, 2 -> 9.3, 4 -> 6.1, 6 -> 6.2, 8 -> 6.3, 16 -> 10.0)")
     ap.add_argument("--hybrid-nccl-frac", type=float, default=0.45, help="--exchange hybrid: share of the rows that travels by NCCL")
     ap.add_argument("--exchange", default="auto", choices=["auto", "gather", "allgather", "p2p", "hybrid"],
                     help="N > 1: auto = p2p when symmetric memory can be set up, else allgather (the line's exchange_used says which); "

@@ -1,7 +1,7 @@
 #!/bin/bash
 # Third set (run under gpurun --gpus N): more pieces per peer for the copy-engine exchange.
 N=${1:-8}; OUT=${2:-gpurun_out}; PORT=29800
-for C in 8 16; do
+for C in ${CHUNKS:-8 16}; do
   PORT=$((PORT + 1))
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT \
       bench.py --gpus $N --steps 8 --warmup 3 --zbuf-images 0 --no-e2e --exchange p2p --p2p-chunks $C > $OUT/r02_scale_n${N}_p2p_chunks$C.log 2> $OUT/r02_scale_n${N}_p2p_chunks$C.err
