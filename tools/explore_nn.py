@@ -5,6 +5,7 @@ usage: explore_nn.py n_cloud n_queries cells xsubs groups [radius|unbounded]
 """
 import os
 import sys
+import zlib
 import numpy as np
 import torch
 
@@ -69,4 +70,5 @@ for env in envs:
                   same = bool(np.array_equal(ref, res))
                   print(f"cell {cell:7.4f} xs {xs:2d} cells {info['n_cells']:>11d} K1 {g:2d}: search {ms / n:8.3f} ms  "
                         f"far {fs / n:6.3f} keysort {ks / n:6.3f} ms  total {(ms + fs + ks) / n:7.3f} ms  "
-                        f"{Q / ((ms + fs) / n) / 1e3:8.1f} Mq/s (search+far)  hits {(res >= 0).mean():.3f} same={same}", flush=True)
+                        f"{Q / ((ms + fs) / n) / 1e3:8.1f} Mq/s (search+far)  hits {(res >= 0).mean():.3f} same={same} "
+                        f"crc {zlib.crc32(res.tobytes()):08x}/{zlib.crc32(d_d2.cpu().numpy().tobytes()):08x}", flush=True)
