@@ -71,56 +71,34 @@ __global__ void k_query_keys(const double* __restrict__ q, RadiusSrc rs, int64_t
   }
 }
 
+// Launch shape and loop knobs, each measured on the bench scene (profiles/r02_nn_variants*.log; rebuild with
+// tools/build_nn_variants.sh to repeat): 128-thread blocks at full occupancy (32 registers) for both kernels; the
+// candidate loop unrolled by four in the search and rolled in the far kernel.
 #ifndef NN_BLOCK
-#define NN_BLOCK 256
+#define NN_BLOCK 128
 #endif
 constexpr int NN_THREADS = NN_BLOCK;
 #ifndef NN_MIN_BLOCKS
-#define NN_MIN_BLOCKS 8
+#define NN_MIN_BLOCKS 16
 #endif
 #ifndef FAR_MIN_BLOCKS
-#define FAR_MIN_BLOCKS 6
+#define FAR_MIN_BLOCKS 16  // 32 registers and spills, but the far kernel is latency-bound: 0.999 ms against 1.009 (12) / 1.057 (10) / 1.175 (8)
 #endif
 #ifndef FAR_DRAW
 #define FAR_DRAW 1         // queue entries a group takes per draw (1 measured best: 1.16 ms vs 1.29 ms at 4)
 #endif
 #ifndef FAR_GROUP
-#define FAR_GROUP 16      // lanes per far query (32, 16 or 8)
-#endif
-#ifndef NN_F32X2
-#define NN_F32X2 0         // 1: packed fp32x2 (sm_100 FADD2 / FMUL2) for the x, y part of a candidate's distance
+#define FAR_GROUP 16      // lanes per far query (32 or 16)
 #endif
 #ifndef NN_UNROLL
-#define NN_UNROLL 4        // unroll factor of the candidate loop in k_nn_search
+#define NN_UNROLL 4        // unroll factor of the candidate loop in k_nn_search (8: 2.86 ms against 2.12)
 #endif
 #ifndef FAR_UNROLL
-#define FAR_UNROLL 4       // ... and in k_nn_far
-#endif
-#ifndef NN_LD256
-#define NN_LD256 0         // 1: k_nn_search scans aligned point pairs with 256-bit loads
-#endif
-#ifndef NN_SCAN4
-#define NN_SCAN4 0         // 1: k_nn_search scans in groups of four with all loads up front
-#endif
-#ifndef FAR_LAZY_MIN
-#define FAR_LAZY_MIN 0     // 1: k_nn_far reduces the (distance, index) pair over the group once per query, the bound on demand
-#endif
-#ifndef NN_KEY_PRELOAD
-#define NN_KEY_PRELOAD 0   // 1: the own cell's run is fetched from the sorted key, in parallel with the record gather
+#define FAR_UNROLL 1       // ... and in k_nn_far (4: 1.08 ms against 1.04)
 #endif
 constexpr int NN_UNROLL_N = NN_UNROLL;
 constexpr float SHRINK = 0.999999f;   // applied to lower bounds before comparing with a float d2
 constexpr float GROW = 1.000001f;
-
-// ((ax - bx)^2, (ay - by)^2), each operation rounded to nearest per half (sub.rn.f32x2, mul.rn.f32x2)
-__device__ __forceinline__ void sq_diff2(float ax, float ay, float bx, float by, float& xx, float& yy) {
-  unsigned long long a, b, d;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(ax), "f"(ay));
-  asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(bx), "f"(by));
-  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  asm("mul.rn.f32x2 %0, %1, %1;" : "=l"(d) : "l"(d));
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(xx), "=f"(yy) : "l"(d));
-}
 
 // Per-query search state.  All geometry is in metres relative to the grid origin.
 struct Query {
@@ -136,17 +114,8 @@ struct Query {
 
   // one candidate: exact float32 (dx^2 + dy^2) + dz^2 of the reference's metric, packed with the point's index
   __device__ __forceinline__ unsigned long long offer(const float4 p, unsigned long long bst) const {
-#if NN_F32X2
-    // x and y halves in one packed instruction each (FADD2, FMUL2): every half is rounded to nearest like the
-    // scalar form, so d is the same float
-    float xx, yy;
-    sq_diff2(qx, qy, p.x, p.y, xx, yy);
-    float ddz = qz - p.z;
-    float d = __fadd_rn(__fadd_rn(xx, yy), __fmul_rn(ddz, ddz));
-#else
     float ddx = qx - p.x, ddy = qy - p.y, ddz = qz - p.z;
     float d = __fadd_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)), __fmul_rn(ddz, ddz));
-#endif
     unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | __float_as_uint(p.w);
     return key < bst ? key : bst;
   }
@@ -163,58 +132,6 @@ struct Query {
       bst = offer(__ldg(&g.pts[j]), bst);
     }
     best = bst;
-  }
-
-  // The same scan of [b, e) with one 256-bit load (sm_100 LDG.E.256) per ALIGNED PAIR of points: an odd first and a
-  // last single point go through 128-bit loads.  Half the load requests of scan() for the same candidates -- the
-  // thread-per-query search is limited by the L1 tag stage (every lane's point lies in another line), not by bytes.
-  __device__ __forceinline__ void scan_pairs(const GridView& g, uint32_t b, uint32_t e) {
-    unsigned long long bst = best;
-    uint32_t j = b;
-    if ((j & 1u) && j < e) { bst = offer(__ldg(&g.pts[j]), bst); j++; }
-#pragma unroll 1
-    for (; j + 2 <= e; j += 2) {
-      PCD_DASSERT(j + 1 < g.n);
-      float4 p0, p1;
-      asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-          : "=f"(p0.x), "=f"(p0.y), "=f"(p0.z), "=f"(p0.w), "=f"(p1.x), "=f"(p1.y), "=f"(p1.z), "=f"(p1.w) : "l"(g.pts + j));
-      bst = offer(p0, bst);
-      bst = offer(p1, bst);
-    }
-    if (j < e) bst = offer(__ldg(&g.pts[j]), bst);
-    best = bst;
-  }
-
-  // The same scan in groups of four whose loads are all issued before the first distance is formed (the compiler's
-  // unroll-by-four peels a remainder of 1..3 points whose loads wait for one another): one memory round trip per
-  // four candidates.  Points beyond e are neither loaded nor offered.
-  __device__ __forceinline__ void scan_groups(const GridView& g, uint32_t b, uint32_t e) {
-    unsigned long long bst = best;
-#pragma unroll 1
-    for (uint32_t j = b; j < e; j += 4) {
-      const float4* p = g.pts + j;
-      const bool v1 = j + 1 < e, v2 = j + 2 < e, v3 = j + 3 < e;
-      PCD_DASSERT(j < g.n);
-      float4 p0 = __ldg(p), p1, p2, p3;                   // p1..p3 stay unset (and unused) beyond e
-      if (v1) p1 = __ldg(p + 1);
-      if (v2) p2 = __ldg(p + 2);
-      if (v3) p3 = __ldg(p + 3);
-      bst = offer(p0, bst);
-      if (v1) bst = offer(p1, bst);
-      if (v2) bst = offer(p2, bst);
-      if (v3) bst = offer(p3, bst);
-    }
-    best = bst;
-  }
-
-  __device__ __forceinline__ void scan1(const GridView& g, uint32_t b, uint32_t e) {
-#if NN_LD256
-    scan_pairs(g, b, e);
-#elif NN_SCAN4
-    scan_groups(g, b, e);
-#else
-    scan(g, b, e, 0, 1);
-#endif
   }
 
   // lower bound (metres) on the distance along one axis from coordinate p to cells [lo, hi] of edge c
@@ -282,13 +199,12 @@ struct Query {
     const uint32_t b = __ldg(&g.cell_start[lin + x0]);
     const uint32_t e = __ldg(&g.cell_start[lin + x1 + 1]);
     PCD_DASSERT(b <= e && e <= g.n);
-    scan1(g, b, e);
+    scan(g, b, e, 0, 1);
   }
 
   // phase 1: own cell, rest of the centre row, then rings 1..K1 of rows; returns true when certified
-  // own_b / own_e: the own cell's run when the caller has fetched it already (have_own)
   template <int K1>
-  __device__ __forceinline__ bool search_block(const GridView& g, bool have_own = false, uint32_t own_b = 0, uint32_t own_e = 0) {
+  __device__ __forceinline__ bool search_block(const GridView& g) {
     const int kx = K1 * g.xs;
     // squared axis gaps to the rows / slabs at offset -K1..K1 (NaN outside the grid -> never scanned)
     float gy2[2 * K1 + 1], gz2[2 * K1 + 1];
@@ -300,17 +216,15 @@ struct Query {
     }
     // own cell, then the rest of the centre row inside the chord of the bound it gave
     const uint32_t lin0 = ((uint32_t)iz * (uint32_t)g.dy + (uint32_t)iy) * (uint32_t)g.dx;
-    uint32_t b0 = own_b, e0 = own_e;
-    if (!have_own) { b0 = __ldg(&g.cell_start[lin0 + ix]); e0 = __ldg(&g.cell_start[lin0 + ix + 1]); }
-    PCD_DASSERT(b0 == g.cell_start[lin0 + ix] && e0 == g.cell_start[lin0 + ix + 1]);
-    scan1(g, b0, e0);
+    const uint32_t b0 = __ldg(&g.cell_start[lin0 + ix]), e0 = __ldg(&g.cell_start[lin0 + ix + 1]);
+    scan(g, b0, e0, 0, 1);
     {
       int x0 = ix - kx, x1 = ix + kx;
       chord(g, bound2(), 0.0f, x0, x1);                    // always contains the own cell
       x0 = min(x0, ix); x1 = max(x1, ix);
       const uint32_t b = __ldg(&g.cell_start[lin0 + x0]), e = __ldg(&g.cell_start[lin0 + x1 + 1]);
-      scan1(g, b, b0);
-      scan1(g, e0, e);
+      scan(g, b, b0, 0, 1);
+      scan(g, e0, e, 0, 1);
     }
 #pragma unroll
     for (int k = 1; k <= K1; k++) {
@@ -338,8 +252,9 @@ struct Query {
 // Every lane of a group holds the same query; the blocks of a Chebyshev shell are spread over the lanes (one
 // occupancy word each), occupied blocks that can still hold a winner are then visited by the whole group in
 // order of increasing box distance: the 64 cells of a block are bounded 64 / FAR_GROUP per lane, and a cell's
-// points are scanned FAR_GROUP at a time with a group-wide min of (d2 bits << 32 | index) after every cell, so
-// the pruning bound is always the group's.  The kernel is bound by the latency of its dependent loads
+// points are scanned FAR_GROUP at a time.  Each lane keeps the best of the points IT has seen; the pruning bound is
+// the group's (a min over the lanes' distance words, refreshed after every cell that improved some lane), and the
+// (distance, index) pairs are reduced over the group once per query.  The kernel is bound by the latency of its dependent loads
 // (occupancy word -> cell_start -> points); FAR_GROUP < 32 puts several independent queries into one warp.
 template <int G>
 struct FarSearch {
@@ -387,18 +302,12 @@ struct FarSearch {
     const uint32_t b = __ldg(&g.cell_start[lin + x0]), e = __ldg(&g.cell_start[lin + x1 + 1]);
     PCD_DASSERT(b <= e && e <= g.n);
     if (b == e) return;
-#if FAR_LAZY_MIN
     // every lane keeps its own best; only the BOUND is the group's, and it is refreshed (a 32-bit min over the
     // distance words) only after a cell in which some lane improved.  The 64-bit (distance, index) min over the
     // lanes is taken once, at the end of run().
     const unsigned long long before = Q.best;
     Q.template scan<FAR_UNROLL>(g, b, e, lane, G);
     if (tile.any(Q.best != before)) b2 = fminf(Q.R2, __uint_as_float(min_u32((unsigned)(Q.best >> 32))));
-#else
-    Q.template scan<FAR_UNROLL>(g, b, e, lane, G);
-    Q.best = min_u64(Q.best);
-    b2 = Q.bound2();
-#endif
   }
 
   // whole group, uniform arguments: the occupied cells of one block in order of increasing box distance
@@ -519,9 +428,7 @@ struct FarSearch {
       const float rc2 = certified2(bx, by, bz, kb);
       if (rc2 == INFINITY || b2 <= rc2) break;
     }
-#if FAR_LAZY_MIN
     Q.best = min_u64(Q.best);
-#endif
   }
 };
 
@@ -561,18 +468,15 @@ struct __align__(16) FarItem { unsigned long long best; uint32_t i; uint32_t pad
 
 template <int K1>
 __global__ void __launch_bounds__(NN_THREADS, NN_MIN_BLOCKS) k_nn_search(GridView g, const float4* __restrict__ qrec,
-                                                          const uint32_t* __restrict__ order, const uint32_t* __restrict__ cell_of,
-                                                          int64_t n, int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
+                                                          const uint32_t* __restrict__ order, int64_t n,
+                                                          int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
                                                           FarItem* __restrict__ far, unsigned int* __restrict__ far_count) {
   const int64_t slot = (int64_t)blockIdx.x * NN_THREADS + threadIdx.x;
   if (slot >= n) return;
   const uint32_t i = order ? order[slot] : (uint32_t)slot;
-  // cell_of[slot] (the sorted key) is the query's own cell: its run can be fetched while the record gather is in flight
-  uint32_t own_b = 0, own_e = 0;
-  if (cell_of) { const uint32_t cell = cell_of[slot]; own_b = __ldg(&g.cell_start[cell]); own_e = __ldg(&g.cell_start[cell + 1]); }
   Query Q;
   const bool valid = Q.load(g, qrec, i);
-  const bool resolved = valid ? Q.search_block<K1>(g, cell_of != nullptr, own_b, own_e) : true;
+  const bool resolved = valid ? Q.search_block<K1>(g) : true;
   if (resolved) nn_write(Q.best, i, idx_out, d2_out);
   // warp-aggregated push of the uncertified queries
   const unsigned act = __activemask();
@@ -630,7 +534,6 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   if (d_opt_num && !sweep) PCD_FAIL(ctx, PCD_E_INVALID, "opt_num given without a range sweep");
   const GridView& g = cloud->grid;
   const uint32_t* order = nullptr;
-  const uint32_t* cell_of = nullptr;
   const char* kenv = getenv("PCD_B200_NN_K1");      // tuning knobs (tools/explore_nn.py)
   const int K1 = kenv ? atoi(kenv) : 1;
   RadiusSrc rs;
@@ -662,9 +565,6 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
       PCD_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
       PCD_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp, kb, vb, (int)n, skip, bits, st));
       order = vb.Current();
-#if NN_KEY_PRELOAD
-      cell_of = kb.Current();
-#endif
     }
   }
   PCD_CUDA(ctx, ctx->far_q.ensure(sizeof(FarItem) * (size_t)n + 16));
@@ -674,8 +574,8 @@ int nn_search_dev(pcd_cloud* cloud, const double* d_q, const double* d_radius, d
   {
     ProfScope ps(ctx, PCD_K_NN_SEARCH, st);
     PCD_CUDA(ctx, cudaMemsetAsync(far_count, 0, 8, st));    // queue length and the work counter of phase 2
-    if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, cell_of, n, d_idx, d2, far, far_count);
-    else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, cell_of, n, d_idx, d2, far, far_count);
+    if (K1 == 2) k_nn_search<2><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
+    else k_nn_search<1><<<blocks, NN_THREADS, 0, st>>>(g, qrec, order, n, d_idx, d2, far, far_count);
     PCD_LAUNCH_CHECK(ctx);
   }
   {
