@@ -259,4 +259,63 @@ int pcd_filter_outliers_batch(pcd_ctx* ctx, const double* p, const double* lidar
   return PCD_OK;
 }
 
+// ---- allocation-free variant of pcd_residual_jacobian_batch_dev --------------------------------------------------
+// For callers that may not allocate device memory (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  The per-block partial sums of sum r^2 -- the one piece of scratch k_resjac needs -- live in a
+// file-scope device array instead of the context's growable buffer: 65 536 doubles = 512 KiB, held by every GPU that
+// loads the library until the process exits.  That bounds one call at 65 536 * 256 = 16 777 216 constraints.
+// All calls on a device share the array and it keeps the last call's contents.  Nothing has to start at zero: block b
+// of a call writes slot b before the one-block sum reads slots [0, blocks), in stream order, so stale slots beyond a
+// call's block count are never read.  Calls that OVERLAP on one GPU (different streams) race on it: serialise them.
+}  // extern "C"
+
+namespace pcd {
+constexpr int64_t NOALLOC_MAX_BLOCKS = 65536;
+constexpr int64_t NOALLOC_MAX_N = NOALLOC_MAX_BLOCKS * RJ_THREADS;
+static __device__ __align__(256) double g_noalloc_partial[NOALLOC_MAX_BLOCKS];
+
+// The array's name is a host-side stand-in in host code, not a device address: its device address is looked up once
+// per device, with that device current, and cached.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+static std::mutex g_noalloc_mu;
+
+static cudaError_t noalloc_scratch(int device, double** out) {       // caller has made `device` current
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    double* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_partial);
+    if (e != cudaSuccess) return e;
+    if (!ptr) return cudaErrorInvalidSymbol;
+    g_noalloc_ptr[device] = ptr;
+  }
+  *out = g_noalloc_ptr[device];
+  return cudaSuccess;
+}
+}  // namespace pcd
+
+extern "C" {
+
+int64_t pcd_residual_jacobian_noalloc_max(void) { return pcd::NOALLOC_MAX_N; }
+
+int pcd_residual_jacobian_batch_dev_noalloc(pcd_ctx* ctx, const double* d_p, const double* d_abcd, const double* d_w, int64_t n,
+                                            double* d_r, double* d_J, double* d_sum_sq, void* stream) {
+  if (!ctx || n < 0 || (n > 0 && (!d_p || !d_abcd || !d_w || !d_r)))
+    PCD_FAIL(ctx, PCD_E_INVALID, "pcd_residual_jacobian_batch_dev_noalloc: bad argument");
+  if (n > pcd::NOALLOC_MAX_N)
+    PCD_FAIL(ctx, PCD_E_INVALID, "pcd_residual_jacobian_batch_dev_noalloc: %lld constraints exceed the fixed scratch (limit %lld per call); "
+             "split the batch or use pcd_residual_jacobian_batch_dev", (long long)n, (long long)pcd::NOALLOC_MAX_N);
+  DeviceGuard g(ctx->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) { if (d_sum_sq) PCD_CUDA(ctx, cudaMemsetAsync(d_sum_sq, 0, 8, st)); return PCD_OK; }
+  const int nb = pcd_blocks(n, pcd::RJ_THREADS);
+  double* partial = nullptr;
+  if (d_sum_sq) PCD_CUDA(ctx, pcd::noalloc_scratch(ctx->device, &partial));
+  pcd::k_resjac<<<nb, pcd::RJ_THREADS, 0, st>>>(d_p, (const double4*)d_abcd, d_w, n, d_r, d_J, partial);
+  PCD_LAUNCH_CHECK(ctx);
+  if (d_sum_sq) { pcd::k_sum_partials<<<1, 256, 0, st>>>(partial, nb, d_sum_sq); PCD_LAUNCH_CHECK(ctx); }
+  return PCD_OK;
+}
+
 }  // extern "C"

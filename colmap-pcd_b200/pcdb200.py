@@ -72,6 +72,8 @@ def lib():
         _lib.pcd_submap_cells.argtypes = [C.c_void_p]
         _lib.pcd_ctx_launches.restype = C.c_int64
         _lib.pcd_ctx_launches.argtypes = [C.c_void_p]
+        _lib.pcd_residual_jacobian_noalloc_max.restype = C.c_int64
+        _lib.pcd_residual_jacobian_noalloc_max.argtypes = []
         _lib.pcd_cloud_device_ptr.restype = C.c_void_p
         _lib.pcd_cloud_device_ptr.argtypes = [C.c_void_p]
         for name in ("pcd_ctx_destroy", "pcd_cloud_destroy", "pcd_host_free", "pcd_free"):
@@ -159,6 +161,13 @@ class Context:
                                                          C.c_int64(n), C.c_void_p(d_r), C.c_void_p(d_J) if d_J else None,
                                                          C.c_void_p(d_sum) if d_sum else None, C.c_void_p(stream)),
                    "pcd_residual_jacobian_batch_dev")
+
+    def residual_jacobian_dev_noalloc(self, d_p, d_abcd, d_w, n, d_r, d_J, d_sum, stream=0):
+        """pcd_residual_jacobian_batch_dev_noalloc: the same evaluation with its scratch in a fixed device array."""
+        self.check(lib().pcd_residual_jacobian_batch_dev_noalloc(self._h, C.c_void_p(d_p), C.c_void_p(d_abcd), C.c_void_p(d_w),
+                                                                 C.c_int64(n), C.c_void_p(d_r), C.c_void_p(d_J) if d_J else None,
+                                                                 C.c_void_p(d_sum) if d_sum else None, C.c_void_p(stream)),
+                   "pcd_residual_jacobian_batch_dev_noalloc")
 
     def residual_pose_jacobian(self, p_cam, qvec, tvec, abcd, w):
         p_cam, qvec, tvec, abcd, w = _f64(p_cam, 3), _f64(qvec, 4), _f64(tvec, 3), _f64(abcd, 4), _f64(w).ravel()

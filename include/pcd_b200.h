@@ -222,6 +222,17 @@ PCD_API int pcd_residual_jacobian_batch(pcd_ctx* ctx, const double* p_xyz, const
                                         int64_t n, double* r, double* J, double* sum_sq);
 PCD_API int pcd_residual_jacobian_batch_dev(pcd_ctx* ctx, const double* d_p_xyz, const double* d_abcd, const double* d_w,
                                             int64_t n, double* d_r, double* d_J, double* d_sum_sq, void* stream);
+/* Allocation-free variant of pcd_residual_jacobian_batch_dev.  No counterpart in the reference: added
+ * for callers that may not allocate device memory (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same arguments, same kernels, bit-identical r / J / sum_sq; the block partial sums
+ * live in a fixed 512 KiB device array inside the library (held by every GPU that loads it until exit), so the call
+ * makes no cudaMalloc / cudaFree and n is limited to pcd_residual_jacobian_noalloc_max() = 16 777 216 constraints per
+ * call -- larger n returns PCD_E_INVALID with a message.  All calls on one device share that array (it keeps the last
+ * call's contents; nothing in it needs clearing): calls that overlap on the GPU race, so issue them in one stream or
+ * order them with events.  Not timed by pcd_ctx_profile. */
+PCD_API int pcd_residual_jacobian_batch_dev_noalloc(pcd_ctx* ctx, const double* d_p_xyz, const double* d_abcd, const double* d_w,
+                                                    int64_t n, double* d_r, double* d_J, double* d_sum_sq, void* stream);
+PCD_API int64_t pcd_residual_jacobian_noalloc_max(void);
 /* fp32 wire format of the residual blocks for the multi-GPU exchange (north_star: "fp32 paths stated separately";
  * no reference counterpart).  d_out[4n] = {r, J0, J1, J2} per constraint, each rounded to nearest float; d_out is
  * 16-byte aligned.  The fp64 blocks are unchanged; this is a transport format only. */
