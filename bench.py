@@ -35,9 +35,9 @@ ALG_BYTES_NN = 260.0       # 12 B query + 8 B result + one 15-po
 # dram__bytes_read.sum + dram__bytes_write.sum of k_nn_search + k_nn_far per launch pair, from the `ncu --set full` capture
 # of the default workload named in NCU_TRAFFIC_SOURCE (the kernels are unchanged since that capture); None for any other
 # workload or size
-NCU_TRAFFIC_NN_SWEEP50M = 5.270e9
-NCU_TRAFFIC_SOURCE = ("profiles/r02_ncu_nn_bench_summary.txt: ncu --set full over this command, round 2 (3.712 + 0.778 GB k_nn_search, "
-                      "0.710 + 0.070 GB k_nn_far, 16 M queries)")
+NCU_TRAFFIC_NN_SWEEP50M = 5.456e9
+NCU_TRAFFIC_SOURCE = ("profiles/r02_ncu_nn_v5_summary.txt: ncu --set full over this command, round 2, shipped kernels (3.759 + 0.788 GB k_nn_search, "
+                      "0.780 + 0.128 GB k_nn_far, 16 M queries)")
 ALG_BYTES_RECORD = 56.0
 ALG_BYTES_RESJAC = 96.0
 WEIGHTS = (10.0, 1000.0, 10000.0)          # proj / icp / icp_ground (src/controllers/incremental_mapper.h:74-78)
