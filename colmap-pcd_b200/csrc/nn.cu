@@ -142,8 +142,18 @@ struct Query {
 
   // x interval [x0, x1] (cells of edge cx) clipped to the chord of the ball of squared radius b2 at
   // squared (y, z) offset g2, and to the grid
+  template <bool APPROX_SQRT = false>
   __device__ __forceinline__ bool chord(const GridView& g, float b2, float g2, int& x0, int& x1) const {
-    float hx = sqrtf(b2 - g2) * GROW + g.margin;          // INFINITY stays INFINITY
+    float hr;
+    if (APPROX_SQRT) {
+      // one MUFU.SQRT (relative error <= 2^-23: GROW covers 8 ulp; a subnormal argument flushes to 0 and the margin alone
+      // covers it) instead of the correctly rounded sequence with its fix-up branch: 0.99 -> 0.96 ms in k_nn_far, where a
+      // chord is cut per visited cell; k_nn_search keeps sqrtf (2.09 -> 2.18 ms with the approximation: more spills)
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(hr) : "f"(b2 - g2));
+    } else {
+      hr = sqrtf(b2 - g2);
+    }
+    float hx = hr * GROW + g.margin;                       // INFINITY stays INFINITY
     x0 = max(max(x0, 0), (int)floorf((px - hx) * g.inv_cx));
     x1 = min(min(x1, g.dx - 1), (int)floorf((px + hx) * g.inv_cx));
     return x0 <= x1;
@@ -296,7 +306,7 @@ struct FarSearch {
     float g2 = (gy * gy + gz * gz) * SHRINK;
     if (!(g2 <= b2)) return;
     int x0 = cxc * g.xs, x1 = x0 + g.xs - 1;
-    if (!Q.chord(g, b2, g2, x0, x1)) return;
+    if (!Q.template chord<true>(g, b2, g2, x0, x1)) return;
     const uint32_t lin = ((uint32_t)cz * (uint32_t)g.dy + (uint32_t)cy) * (uint32_t)g.dx;
     PCD_DASSERT(x0 >= 0 && x1 < g.dx && cy >= 0 && cy < g.dy && cz >= 0 && cz < g.dz);
     const uint32_t b = __ldg(&g.cell_start[lin + x0]), e = __ldg(&g.cell_start[lin + x1 + 1]);
